@@ -1,0 +1,55 @@
+/*
+ * whisper_b200.h — additive extensions of libwhisper_b200.so.  Nothing here changes the whisper.h ABI;
+ * a caller that only knows whisper.h never needs this header.
+ *
+ *  - whisper_b200_full_batch: explicit cross-state batching of the transcription path (SURVEY.md §8b
+ *    "proposed additive extension"): N states of one context advance in lock-step, so the encoder runs
+ *    over N windows per launch and every decoder step streams the weights once for all N sequences.
+ *    Semantics per state are exactly those of whisper_full_with_state (reference: wc:6795-7711).
+ *  - stage probes used by the parity tests (the reference keeps these values in whisper_state:
+ *    mel wc:896, embd_enc wc:912, kv_cross wc:891) and launch counters used by bench.py.
+ */
+#ifndef WHISPER_B200_H
+#define WHISPER_B200_H
+
+#include "whisper.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Runs whisper_full_with_state for n states of `ctx` as one batch. samples[i] / n_samples[i] is the PCM of state i.
+ * Returns 0, or the first non-zero per-state code of whisper_full_with_state. */
+WHISPER_API int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
+                                        struct whisper_full_params params, const float * const * samples, const int * n_samples);
+
+/* Batched stage entry points (same contracts as whisper_encode_with_state / whisper_decode_with_state, wc:3933-3971). */
+WHISPER_API int whisper_b200_encode_batch(struct whisper_context * ctx, struct whisper_state ** states, const int * offsets, int n_states);
+/* one new token per state at position n_past[i]; logits readable through whisper_get_logits_from_state */
+WHISPER_API int whisper_b200_decode_batch(struct whisper_context * ctx, struct whisper_state ** states, const whisper_token * tokens,
+                                          const int * n_past, int n_states);
+
+/* Probes: copy a stage output to host memory.  Return the element count (or -1); copy only when cap is large enough. */
+WHISPER_API int64_t whisper_b200_get_mel(struct whisper_state * state, float * dst, int64_t cap, int * n_len, int * n_len_org, int * n_mel);
+WHISPER_API int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int window, float * dst, int64_t cap);   /* [n_ctx][n_state] */
+WHISPER_API int64_t whisper_b200_get_kv_cross(struct whisper_state * state, uint16_t * dst, int64_t cap);            /* f16 [L][2H][T][64] */
+WHISPER_API int64_t whisper_b200_get_aheads_qk(struct whisper_state * state, float * dst, int64_t cap);              /* [n_heads][n_tok][T] */
+WHISPER_API void whisper_b200_get_counters(struct whisper_state * state, int32_t * counts7, int64_t * us6);          /* wc:868-881 */
+
+/* number of kernels this library has launched in this process (all contexts) */
+WHISPER_API uint64_t whisper_b200_kernel_launches(void);
+WHISPER_API void whisper_b200_device_sync(struct whisper_context * ctx);
+
+/* Kernel-level test/bench hooks on raw DEVICE pointers (plain pointers and sizes; used by tests/ and bench.py). */
+/* C[m][n] (f32 or f16) = sum_k A[m][k] * B[n][k], f16 row-major operands, optional f32 bias[n]. Returns 0 on success. */
+WHISPER_API int whisper_b200_test_gemm(const void * a_f16, const void * b_f16, void * c, int m, int n, int k, int lda, int ldb, int ldc,
+                                       int c_is_f16, const float * bias, int block_n);
+/* log-mel of device PCM -> device mel [n_mel][n_len] using the context's filterbank */
+WHISPER_API int whisper_b200_test_mel(struct whisper_context * ctx, const float * d_pcm, int n_samples, float * d_mel);
+/* the decode-step cross-attention kernel on device buffers: q f16 [n][S], kv f16 [2H][T][64] per row (same kv for all rows) */
+WHISPER_API int whisper_b200_test_cross_attn(const void * q_f16, const void * kv_f16, void * out_f16, int n_rows, int n_head, int n_ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,788 @@
+// extern "C" boundary: every symbol include/whisper.h and include/whisper_b200.h declare.
+// Thin argument checking + locking; the work lives in engine.cu / full.cu.  No C++ exception crosses this file.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <regex>
+#include <thread>
+
+#include "../../include/whisper_b200.h"
+#include "engine.h"
+#include "log.h"
+
+using namespace wb;
+
+static_assert(sizeof(whisper_full_params) == 296, "whisper_full_params must be 296 bytes (SURVEY.md 8b)");
+static_assert(sizeof(whisper_context_params) == 48, "whisper_context_params must be 48 bytes");
+static_assert(sizeof(whisper_token_data) == 56, "whisper_token_data must be 56 bytes");
+static_assert(offsetof(whisper_full_params, language) == 96 && offsetof(whisper_full_params, greedy) == 136 &&
+                  offsetof(whisper_full_params, new_segment_callback) == 152 && offsetof(whisper_full_params, grammar_rules) == 232 &&
+                  offsetof(whisper_full_params, vad) == 260 && offsetof(whisper_full_params, vad_params) == 272,
+              "whisper_full_params layout drifted from the reference header");
+
+#define WB_TRY try {
+#define WB_CATCH(retval)                                                        \
+    }                                                                           \
+    catch (const std::exception & e) {                                          \
+        wb::log_error("%s: exception: %s\n", __func__, e.what());               \
+        return retval;                                                          \
+    }                                                                           \
+    catch (...) {                                                               \
+        wb::log_error("%s: unknown exception\n", __func__);                     \
+        return retval;                                                          \
+    }
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------------
+// logging + ggml leakage
+// ---------------------------------------------------------------------------------------------
+void whisper_log_set(ggml_log_callback log_callback, void * user_data) { wb::log_set((wb::wb_log_callback) log_callback, user_data); }
+void ggml_log_set(ggml_log_callback, void *) {}  // no ggml inside: accepted for the crate's install_logging_hooks (src/lib.rs:67-70)
+int ggml_cpu_has_avx(void) { return __builtin_cpu_supports("avx") ? 1 : 0; }
+int ggml_cpu_has_avx2(void) { return __builtin_cpu_supports("avx2") ? 1 : 0; }
+int ggml_cpu_has_fma(void) { return __builtin_cpu_supports("fma") ? 1 : 0; }
+int ggml_cpu_has_f16c(void) { return __builtin_cpu_supports("f16c") ? 1 : 0; }
+
+const char * whisper_print_system_info(void) {
+    static std::string s;
+    s = "WHISPER : COREML = 0 | OPENVINO = 0 | B200 : ARCH = sm_100a | TCGEN05 = 1 | TMA = 1 | CPU_FALLBACK = 0 | ";
+    return s.c_str();
+}
+
+// ---------------------------------------------------------------------------------------------
+// defaults (wc:3622-3638, 5914-6019)
+// ---------------------------------------------------------------------------------------------
+struct whisper_context_params whisper_context_default_params(void) {
+    struct whisper_context_params r;
+    memset(&r, 0, sizeof(r));
+    r.use_gpu = true;
+    r.flash_attn = false;
+    r.gpu_device = 0;
+    r.dtw_token_timestamps = false;
+    r.dtw_aheads_preset = WHISPER_AHEADS_NONE;
+    r.dtw_n_top = -1;
+    r.dtw_aheads.n_heads = 0;
+    r.dtw_aheads.heads = NULL;
+    r.dtw_mem_size = 1024 * 1024 * 128;
+    return r;
+}
+
+struct whisper_vad_params whisper_vad_default_params(void) {  // wc:4384-4395
+    struct whisper_vad_params r;
+    r.threshold = 0.5f;
+    r.min_speech_duration_ms = 250;
+    r.min_silence_duration_ms = 100;
+    r.max_speech_duration_s = 3.4028234663852886e38f;
+    r.speech_pad_ms = 30;
+    r.samples_overlap = 0.1f;
+    return r;
+}
+
+struct whisper_full_params whisper_full_default_params(enum whisper_sampling_strategy strategy) {
+    struct whisper_full_params r;
+    memset(&r, 0, sizeof(r));
+    r.strategy = strategy;
+    r.n_threads = std::min(4, (int) std::thread::hardware_concurrency());
+    r.n_max_text_ctx = 16384;
+    r.no_context = true;
+    r.print_progress = true;
+    r.print_timestamps = true;
+    r.thold_pt = 0.01f;
+    r.thold_ptsum = 0.01f;
+    r.language = "en";
+    r.suppress_blank = true;
+    r.temperature = 0.0f;
+    r.max_initial_ts = 1.0f;
+    r.length_penalty = -1.0f;
+    r.temperature_inc = 0.2f;
+    r.entropy_thold = 2.4f;
+    r.logprob_thold = -1.0f;
+    r.no_speech_thold = 0.6f;
+    r.greedy.best_of = -1;
+    r.beam_search.beam_size = -1;
+    r.beam_search.patience = -1.0f;
+    r.grammar_penalty = 100.0f;
+    r.vad_params = whisper_vad_default_params();
+    if (strategy == WHISPER_SAMPLING_GREEDY) r.greedy.best_of = 5;
+    if (strategy == WHISPER_SAMPLING_BEAM_SEARCH) {
+        r.beam_search.beam_size = 5;
+        r.beam_search.patience = -1.0f;
+    }
+    return r;
+}
+
+struct whisper_context_params * whisper_context_default_params_by_ref(void) {
+    struct whisper_context_params * p = new whisper_context_params;
+    *p = whisper_context_default_params();
+    return p;
+}
+struct whisper_full_params * whisper_full_default_params_by_ref(enum whisper_sampling_strategy strategy) {
+    struct whisper_full_params * p = new whisper_full_params;
+    *p = whisper_full_default_params(strategy);
+    return p;
+}
+void whisper_free_params(struct whisper_full_params * params) { delete params; }
+void whisper_free_context_params(struct whisper_context_params * params) { delete params; }
+
+// ---------------------------------------------------------------------------------------------
+// init / free (wc:3640-3889)
+// ---------------------------------------------------------------------------------------------
+struct whisper_context * whisper_init_with_params_no_state(struct whisper_model_loader * loader, struct whisper_context_params params) {
+    WB_TRY
+    if (!loader || !loader->read) return nullptr;
+    if (params.flash_attn && params.dtw_token_timestamps) {
+        // the reference drops DTW under flash attention (wc:3724-3727); this library's attention always exposes the
+        // alignment-head softmax rows, so the request is honoured
+        log_msg(GGML_LOG_LEVEL_INFO, "%s: flash_attn is a no-op here; dtw_token_timestamps stays enabled\n", __func__);
+    }
+    Context * c = context_create(loader, params);
+    if (!c) {
+        if (loader->close) loader->close(loader->context);
+        return nullptr;
+    }
+    return static_cast<whisper_context *>(c);
+    WB_CATCH(nullptr)
+}
+
+struct whisper_context * whisper_init_from_file_with_params_no_state(const char * path_model, struct whisper_context_params params) {
+    if (!path_model) return nullptr;
+    log_msg(GGML_LOG_LEVEL_INFO, "%s: loading model from '%s'\n", __func__, path_model);
+    FILE * f = fopen(path_model, "rb");
+    if (!f) {
+        log_error("%s: failed to open '%s'\n", __func__, path_model);
+        return nullptr;
+    }
+    whisper_model_loader loader = {};
+    loader.context = f;
+    loader.read = [](void * ctx, void * output, size_t read_size) { return fread(output, 1, read_size, (FILE *) ctx); };
+    loader.eof = [](void * ctx) { return feof((FILE *) ctx) != 0; };
+    loader.close = [](void * ctx) { (void) ctx; };
+    whisper_context * c = whisper_init_with_params_no_state(&loader, params);
+    fclose(f);
+    if (c) c->path_model = path_model;
+    return c;
+}
+
+struct whisper_context * whisper_init_from_buffer_with_params_no_state(void * buffer, size_t buffer_size, struct whisper_context_params params) {
+    if (!buffer) return nullptr;
+    struct buf_context {
+        uint8_t * buffer;
+        size_t size, off;
+    } bc = {(uint8_t *) buffer, buffer_size, 0};
+    log_msg(GGML_LOG_LEVEL_INFO, "%s: loading model from buffer\n", __func__);
+    whisper_model_loader loader = {};
+    loader.context = &bc;
+    loader.read = [](void * ctx, void * output, size_t read_size) {
+        buf_context * b = (buf_context *) ctx;
+        const size_t n = b->off + read_size <= b->size ? read_size : b->size - b->off;
+        memcpy(output, b->buffer + b->off, n);
+        b->off += n;
+        return n;
+    };
+    loader.eof = [](void * ctx) {
+        buf_context * b = (buf_context *) ctx;
+        return b->off >= b->size;
+    };
+    loader.close = [](void *) {};
+    return whisper_init_with_params_no_state(&loader, params);
+}
+
+struct whisper_state * whisper_init_state(struct whisper_context * ctx) {
+    WB_TRY
+    if (!ctx) return nullptr;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    State * s = state_create(ctx);
+    return static_cast<whisper_state *>(s);
+    WB_CATCH(nullptr)
+}
+
+static whisper_context * with_default_state(whisper_context * ctx) {
+    if (!ctx) return nullptr;
+    ctx->state = whisper_init_state(ctx);
+    if (!ctx->state) {
+        whisper_free(ctx);
+        return nullptr;
+    }
+    return ctx;
+}
+struct whisper_context * whisper_init_from_file_with_params(const char * path_model, struct whisper_context_params params) {
+    return with_default_state(whisper_init_from_file_with_params_no_state(path_model, params));
+}
+struct whisper_context * whisper_init_from_buffer_with_params(void * buffer, size_t buffer_size, struct whisper_context_params params) {
+    return with_default_state(whisper_init_from_buffer_with_params_no_state(buffer, buffer_size, params));
+}
+struct whisper_context * whisper_init_with_params(struct whisper_model_loader * loader, struct whisper_context_params params) {
+    return with_default_state(whisper_init_with_params_no_state(loader, params));
+}
+struct whisper_context * whisper_init_from_file(const char * p) { return whisper_init_from_file_with_params(p, whisper_context_default_params()); }
+struct whisper_context * whisper_init_from_buffer(void * b, size_t n) { return whisper_init_from_buffer_with_params(b, n, whisper_context_default_params()); }
+struct whisper_context * whisper_init(struct whisper_model_loader * l) { return whisper_init_with_params(l, whisper_context_default_params()); }
+struct whisper_context * whisper_init_from_file_no_state(const char * p) { return whisper_init_from_file_with_params_no_state(p, whisper_context_default_params()); }
+struct whisper_context * whisper_init_from_buffer_no_state(void * b, size_t n) { return whisper_init_from_buffer_with_params_no_state(b, n, whisper_context_default_params()); }
+struct whisper_context * whisper_init_no_state(struct whisper_model_loader * l) { return whisper_init_with_params_no_state(l, whisper_context_default_params()); }
+
+void whisper_free_state(struct whisper_state * state) {
+    if (!state) return;
+    if (state->ctx) {
+        std::lock_guard<std::mutex> lk(state->ctx->mu);
+        cudaSetDevice(state->ctx->model.device);
+        cudaStreamSynchronize(state->ctx->stream);
+        delete state;
+    } else {
+        delete state;
+    }
+}
+void whisper_free(struct whisper_context * ctx) {
+    if (!ctx) return;
+    if (ctx->state) whisper_free_state(static_cast<whisper_state *>(ctx->state));
+    ctx->state = nullptr;
+    delete ctx;
+}
+
+int whisper_ctx_init_openvino_encoder_with_state(struct whisper_context *, struct whisper_state *, const char *, const char *, const char *) { return 1; }
+int whisper_ctx_init_openvino_encoder(struct whisper_context *, const char *, const char *, const char *) { return 1; }
+
+// ---------------------------------------------------------------------------------------------
+// stage entry points (wc:3891-3971)
+// ---------------------------------------------------------------------------------------------
+int whisper_pcm_to_mel_with_state(struct whisper_context * ctx, struct whisper_state * state, const float * samples, int n_samples, int) {
+    WB_TRY
+    if (!ctx || !state || !samples || n_samples < 0) return -1;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!stage_pcm_to_mel(*state, samples, n_samples)) {
+        log_error("%s: failed to compute mel spectrogram\n", __func__);
+        return -1;
+    }
+    return 0;
+    WB_CATCH(-1)
+}
+int whisper_pcm_to_mel(struct whisper_context * ctx, const float * samples, int n_samples, int n_threads) {
+    return ctx && ctx->state ? whisper_pcm_to_mel_with_state(ctx, static_cast<whisper_state *>(ctx->state), samples, n_samples, n_threads) : -1;
+}
+
+int whisper_set_mel_with_state(struct whisper_context * ctx, struct whisper_state * state, const float * data, int n_len, int n_mel) {
+    WB_TRY
+    if (!ctx || !state || !data) return -1;
+    if (n_mel != ctx->model.filters_n_mel) {
+        log_error("%s: invalid number of mel bands: %d (expected %d)\n", __func__, n_mel, ctx->model.filters_n_mel);
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return stage_set_mel(*state, data, n_len, n_mel) ? 0 : -1;
+    WB_CATCH(-1)
+}
+int whisper_set_mel(struct whisper_context * ctx, const float * data, int n_len, int n_mel) {
+    return ctx && ctx->state ? whisper_set_mel_with_state(ctx, static_cast<whisper_state *>(ctx->state), data, n_len, n_mel) : -1;
+}
+
+int whisper_encode_with_state(struct whisper_context * ctx, struct whisper_state * state, int offset, int) {
+    WB_TRY
+    if (!ctx || !state) return -1;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    State * sp = state;
+    if (!stage_encode(*ctx, &sp, &offset, 1)) {
+        log_error("%s: failed to eval\n", __func__);
+        return -1;
+    }
+    return 0;
+    WB_CATCH(-1)
+}
+int whisper_encode(struct whisper_context * ctx, int offset, int n_threads) {
+    return ctx && ctx->state ? whisper_encode_with_state(ctx, static_cast<whisper_state *>(ctx->state), offset, n_threads) : -1;
+}
+
+int whisper_decode_with_state(struct whisper_context * ctx, struct whisper_state * state, const whisper_token * tokens, int n_tokens, int n_past,
+                              int) {
+    WB_TRY
+    if (!ctx || !state || !tokens || n_tokens <= 0) return 1;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::vector<BatchRow> rows;
+    for (int i = 0; i < n_tokens; ++i) {
+        if (tokens[i] < 0 || tokens[i] >= ctx->model.hp.n_vocab || n_past + i >= ctx->model.hp.n_text_ctx) {
+            log_error("%s: token %d / position %d out of range\n", __func__, tokens[i], n_past + i);
+            return 1;
+        }
+        rows.push_back(BatchRow{state, tokens[i], n_past + i, 0, i == n_tokens - 1});  // whisper_batch_prep_legacy wc:544-556
+    }
+    state->kv_self.seq_rm(0, n_past, -1);
+    if (!stage_decode(*ctx, rows.data(), n_tokens, false) || !stage_fetch_logits(*ctx, rows.data(), n_tokens)) {
+        log_error("%s: failed to eval\n", __func__);
+        return 1;
+    }
+    return 0;
+    WB_CATCH(1)
+}
+int whisper_decode(struct whisper_context * ctx, const whisper_token * tokens, int n_tokens, int n_past, int n_threads) {
+    if (!ctx || ctx->state == nullptr) {
+        log_error("%s: ERROR state was not loaded.\n", __func__);
+        return -1;
+    }
+    return whisper_decode_with_state(ctx, static_cast<whisper_state *>(ctx->state), tokens, n_tokens, n_past, n_threads);
+}
+
+// ---------------------------------------------------------------------------------------------
+// F6: tokenizer (wc:3288-3336, 3973-3988): GPT-2 style regex pre-split, then greedy longest match
+// ---------------------------------------------------------------------------------------------
+static std::vector<int> tokenize_text(const Vocab & vocab, const std::string & text) {
+    std::vector<std::string> words;
+    {
+        std::string str = text;
+        const std::string pat = R"('s|'t|'re|'ve|'m|'ll|'d| ?[[:alpha:]]+| ?[[:digit:]]+| ?[^\s[:alpha:][:digit:]]+|\s+(?!\S)|\s+)";
+        std::regex re(pat);
+        std::smatch m;
+        while (std::regex_search(str, m, re)) {
+            for (auto x : m) words.push_back(x);
+            str = m.suffix();
+        }
+    }
+    std::vector<int> tokens;
+    for (const auto & word : words) {
+        if (word.empty()) continue;
+        int i = 0;
+        const int n = (int) word.size();
+        while (i < n) {
+            int j = n;
+            bool found = false;
+            while (j > i) {
+                auto it = vocab.token_to_id.find(word.substr((size_t) i, (size_t) (j - i)));
+                if (it != vocab.token_to_id.end()) {
+                    tokens.push_back(it->second);
+                    i = j;
+                    found = true;
+                    break;
+                }
+                --j;
+            }
+            if (!found) {
+                log_error("unknown token\n");
+                ++i;
+            }
+        }
+    }
+    return tokens;
+}
+
+int whisper_tokenize(struct whisper_context * ctx, const char * text, whisper_token * tokens, int n_max_tokens) {
+    WB_TRY
+    if (!ctx || !text) return -1;
+    const auto res = tokenize_text(ctx->model.vocab, text);
+    if (n_max_tokens < (int) res.size()) {
+        log_error("%s: too many resulting tokens: %d (max %d)\n", __func__, (int) res.size(), n_max_tokens);
+        return -(int) res.size();
+    }
+    for (int i = 0; i < (int) res.size(); i++) tokens[i] = res[(size_t) i];
+    return (int) res.size();
+    WB_CATCH(-1)
+}
+int whisper_token_count(struct whisper_context * ctx, const char * text) { return -whisper_tokenize(ctx, text, NULL, 0); }
+
+int whisper_lang_max_id(void) { return 99; }
+int whisper_lang_id(const char * lang) {
+    const int id = wb::lang_id(lang);
+    if (id < 0) log_error("%s: unknown language '%s'\n", __func__, lang ? lang : "(null)");
+    return id;
+}
+const char * whisper_lang_str(int id) {
+    if (id < 0 || id >= 100) {
+        log_error("%s: unknown language id %d\n", __func__, id);
+        return nullptr;
+    }
+    return g_langs[id].code;
+}
+const char * whisper_lang_str_full(int id) {
+    if (id < 0 || id >= 100) {
+        log_error("%s: unknown language id %d\n", __func__, id);
+        return nullptr;
+    }
+    return g_langs[id].name;
+}
+
+int whisper_lang_auto_detect_with_state(struct whisper_context * ctx, struct whisper_state * state, int offset_ms, int, float * lang_probs) {
+    WB_TRY
+    if (!ctx || !state) return -1;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return lang_auto_detect(ctx, state, offset_ms, lang_probs);
+    WB_CATCH(-1)
+}
+int whisper_lang_auto_detect(struct whisper_context * ctx, int offset_ms, int n_threads, float * lang_probs) {
+    return ctx && ctx->state ? whisper_lang_auto_detect_with_state(ctx, static_cast<whisper_state *>(ctx->state), offset_ms, n_threads, lang_probs) : -1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// model info / tokens (wc:4185-4259)
+// ---------------------------------------------------------------------------------------------
+int whisper_n_len_from_state(struct whisper_state * state) { return state ? state->n_len_org : 0; }
+int whisper_n_len(struct whisper_context * ctx) { return ctx && ctx->state ? ctx->state->n_len_org : 0; }
+int whisper_n_vocab(struct whisper_context * ctx) { return ctx->model.vocab.n_vocab; }
+int whisper_n_text_ctx(struct whisper_context * ctx) { return ctx->model.hp.n_text_ctx; }
+int whisper_n_audio_ctx(struct whisper_context * ctx) { return ctx->model.hp.n_audio_ctx; }
+int whisper_is_multilingual(struct whisper_context * ctx) { return ctx->model.vocab.is_multilingual() ? 1 : 0; }
+int whisper_model_n_vocab(struct whisper_context * ctx) { return ctx->model.hp.n_vocab; }
+int whisper_model_n_audio_ctx(struct whisper_context * ctx) { return ctx->model.hp.n_audio_ctx; }
+int whisper_model_n_audio_state(struct whisper_context * ctx) { return ctx->model.hp.n_audio_state; }
+int whisper_model_n_audio_head(struct whisper_context * ctx) { return ctx->model.hp.n_audio_head; }
+int whisper_model_n_audio_layer(struct whisper_context * ctx) { return ctx->model.hp.n_audio_layer; }
+int whisper_model_n_text_ctx(struct whisper_context * ctx) { return ctx->model.hp.n_text_ctx; }
+int whisper_model_n_text_state(struct whisper_context * ctx) { return ctx->model.hp.n_text_state; }
+int whisper_model_n_text_head(struct whisper_context * ctx) { return ctx->model.hp.n_text_head; }
+int whisper_model_n_text_layer(struct whisper_context * ctx) { return ctx->model.hp.n_text_layer; }
+int whisper_model_n_mels(struct whisper_context * ctx) { return ctx->model.hp.n_mels; }
+int whisper_model_ftype(struct whisper_context * ctx) { return ctx->model.hp.ftype; }
+int whisper_model_type(struct whisper_context * ctx) { return ctx->model.model_type; }
+const char * whisper_model_type_readable(struct whisper_context * ctx) {
+    static const char * names[] = {"unknown", "tiny", "base", "small", "medium", "large"};
+    const int t = ctx->model.model_type;
+    return names[t >= 0 && t <= 5 ? t : 0];
+}
+float * whisper_get_logits_from_state(struct whisper_state * state) { return state ? state->logits.data() : nullptr; }
+float * whisper_get_logits(struct whisper_context * ctx) { return ctx && ctx->state ? ctx->state->logits.data() : nullptr; }
+const char * whisper_token_to_str(struct whisper_context * ctx, whisper_token token) {
+    const auto & v = ctx->model.vocab.id_to_token;
+    if (token < 0 || token >= (int) v.size()) {
+        log_error("%s: token %d out of range\n", __func__, token);  // the reference throws std::out_of_range here (wc:4218)
+        return "";
+    }
+    return v[(size_t) token].c_str();
+}
+whisper_token whisper_token_eot(struct whisper_context * ctx) { return ctx->model.vocab.token_eot; }
+whisper_token whisper_token_sot(struct whisper_context * ctx) { return ctx->model.vocab.token_sot; }
+whisper_token whisper_token_solm(struct whisper_context * ctx) { return ctx->model.vocab.token_solm; }
+whisper_token whisper_token_prev(struct whisper_context * ctx) { return ctx->model.vocab.token_prev; }
+whisper_token whisper_token_nosp(struct whisper_context * ctx) { return ctx->model.vocab.token_nosp; }
+whisper_token whisper_token_not(struct whisper_context * ctx) { return ctx->model.vocab.token_not; }
+whisper_token whisper_token_beg(struct whisper_context * ctx) { return ctx->model.vocab.token_beg; }
+whisper_token whisper_token_lang(struct whisper_context * ctx, int lang_id) { return ctx->model.vocab.token_sot + 1 + lang_id; }
+whisper_token whisper_token_translate(struct whisper_context * ctx) { return ctx->model.vocab.token_translate; }
+whisper_token whisper_token_transcribe(struct whisper_context * ctx) { return ctx->model.vocab.token_transcribe; }
+
+// ---------------------------------------------------------------------------------------------
+// timings (wc:4261-4312): like the reference these read ctx->state, which is NULL for *_no_state contexts
+// ---------------------------------------------------------------------------------------------
+struct whisper_timings * whisper_get_timings(struct whisper_context * ctx) {
+    if (!ctx || ctx->state == nullptr) return nullptr;
+    const State & s = *ctx->state;
+    whisper_timings * t = new whisper_timings;
+    t->sample_ms = 1e-3f * s.t_sample_us / std::max(1, s.n_sample);
+    t->encode_ms = 1e-3f * s.t_encode_us / std::max(1, s.n_encode);
+    t->decode_ms = 1e-3f * s.t_decode_us / std::max(1, s.n_decode);
+    t->batchd_ms = 1e-3f * s.t_batchd_us / std::max(1, s.n_batchd);
+    t->prompt_ms = 1e-3f * s.t_prompt_us / std::max(1, s.n_prompt);
+    return t;
+}
+void whisper_print_timings(struct whisper_context * ctx) {
+    if (!ctx) return;
+    const int64_t t_end_us = time_us();
+    log_msg(GGML_LOG_LEVEL_INFO, "\n");
+    log_msg(GGML_LOG_LEVEL_INFO, "%s:     load time = %8.2f ms\n", __func__, ctx->t_load_us / 1000.0f);
+    if (ctx->state != nullptr) {
+        const State & s = *ctx->state;
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:     fallbacks = %3d p / %3d h\n", __func__, s.n_fail_p, s.n_fail_h);
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:      mel time = %8.2f ms\n", __func__, s.t_mel_us / 1000.0f);
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:   sample time = %8.2f ms / %5d runs\n", __func__, 1e-3f * s.t_sample_us, std::max(1, s.n_sample));
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:   encode time = %8.2f ms / %5d runs\n", __func__, 1e-3f * s.t_encode_us, std::max(1, s.n_encode));
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:   decode time = %8.2f ms / %5d runs\n", __func__, 1e-3f * s.t_decode_us, std::max(1, s.n_decode));
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:   batchd time = %8.2f ms / %5d runs\n", __func__, 1e-3f * s.t_batchd_us, std::max(1, s.n_batchd));
+        log_msg(GGML_LOG_LEVEL_INFO, "%s:   prompt time = %8.2f ms / %5d runs\n", __func__, 1e-3f * s.t_prompt_us, std::max(1, s.n_prompt));
+    }
+    log_msg(GGML_LOG_LEVEL_INFO, "%s:    total time = %8.2f ms\n", __func__, (t_end_us - ctx->t_start_us) / 1000.0f);
+}
+void whisper_reset_timings(struct whisper_context * ctx) {
+    if (!ctx) return;
+    ctx->t_start_us = time_us();
+    if (ctx->state != nullptr) {
+        State & s = *ctx->state;
+        s.t_mel_us = s.t_sample_us = s.t_encode_us = s.t_decode_us = s.t_batchd_us = s.t_prompt_us = 0;
+        s.n_sample = s.n_encode = s.n_decode = s.n_batchd = s.n_prompt = 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// full transcription (wc:6795-7864) and result accessors (wc:7866-8033)
+// ---------------------------------------------------------------------------------------------
+int whisper_full_with_state(struct whisper_context * ctx, struct whisper_state * state, struct whisper_full_params params, const float * samples,
+                            int n_samples) {
+    WB_TRY
+    if (!ctx || !state) return -1;
+    if (params.vad) log_msg(GGML_LOG_LEVEL_WARN, "%s: the VAD front end is outside this library's path; processing all samples\n", __func__);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    State * sp = state;
+    return full_with_states(ctx, &sp, 1, &params, false, &samples, &n_samples);
+    WB_CATCH(-1)
+}
+int whisper_full(struct whisper_context * ctx, struct whisper_full_params params, const float * samples, int n_samples) {
+    if (!ctx || !ctx->state) return -1;
+    return whisper_full_with_state(ctx, static_cast<whisper_state *>(ctx->state), params, samples, n_samples);
+}
+
+int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state ** states, int n_states, struct whisper_full_params params,
+                            const float * const * samples, const int * n_samples) {
+    WB_TRY
+    if (!ctx || !states || n_states <= 0 || !samples || !n_samples) return -1;
+    std::vector<State *> sp((size_t) n_states);
+    for (int i = 0; i < n_states; ++i) {
+        if (!states[i] || states[i]->ctx != ctx) return -1;
+        for (int j = 0; j < i; ++j)
+            if (states[j] == states[i]) return -1;
+        sp[(size_t) i] = states[i];
+    }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return full_with_states(ctx, sp.data(), n_states, &params, false, samples, n_samples);
+    WB_CATCH(-1)
+}
+
+// whisper_full_parallel (wc:7736-7864): equal sample spans, one state per span — here the spans advance as ONE batch on
+// the device instead of one CPU thread each; the merge rule (time offsets, clamping, append order) is the reference's.
+int whisper_full_parallel(struct whisper_context * ctx, struct whisper_full_params params, const float * samples, int n_samples, int n_processors) {
+    WB_TRY
+    if (!ctx || !ctx->state) return -1;
+    if (n_processors <= 1) return whisper_full(ctx, params, samples, n_samples);
+    const int offset_samples = (WHISPER_SAMPLE_RATE * params.offset_ms) / 1000;
+    const int n_per = (n_samples - offset_samples) / n_processors;
+    std::vector<whisper_state *> extra;
+    std::vector<State *> sp;
+    std::vector<whisper_full_params> ps;
+    std::vector<const float *> smp;
+    std::vector<int> ns;
+    {
+        auto p0 = params;
+        p0.print_realtime = false;
+        sp.push_back(ctx->state);
+        ps.push_back(p0);
+        smp.push_back(samples);
+        ns.push_back(offset_samples + n_per);
+    }
+    for (int i = 0; i < n_processors - 1; ++i) {
+        whisper_state * s = whisper_init_state(ctx);
+        if (!s) {
+            for (auto * e : extra) whisper_free_state(e);
+            return -1;
+        }
+        extra.push_back(s);
+        const int start = offset_samples + (i + 1) * n_per;
+        const int n_cur = (i == n_processors - 2) ? n_samples - start : n_per;
+        auto pc = params;
+        pc.offset_ms = 0;
+        pc.print_progress = false;
+        pc.print_realtime = false;
+        pc.new_segment_callback = nullptr;
+        pc.new_segment_callback_user_data = nullptr;
+        pc.progress_callback = nullptr;
+        pc.progress_callback_user_data = nullptr;
+        sp.push_back(s);
+        ps.push_back(pc);
+        smp.push_back(samples + start);
+        ns.push_back(n_cur);
+    }
+    int ret;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        ret = full_with_states(ctx, sp.data(), (int) sp.size(), ps.data(), true, smp.data(), ns.data());
+    }
+    const int64_t offset_t = (int64_t) (params.offset_ms / 10.0);
+    State & main = *ctx->state;
+    for (int i = 0; i < n_processors - 1; ++i) {
+        for (auto & r : extra[(size_t) i]->result_all) {
+            r.t0 += 100 * ((i + 1) * n_per) / WHISPER_SAMPLE_RATE + offset_t;
+            r.t1 += 100 * ((i + 1) * n_per) / WHISPER_SAMPLE_RATE + offset_t;
+            if (!main.result_all.empty()) r.t0 = std::max(r.t0, main.result_all.back().t1);
+            main.result_all.push_back(std::move(r));
+            if (params.new_segment_callback)
+                params.new_segment_callback(ctx, static_cast<whisper_state *>(ctx->state), 1, params.new_segment_callback_user_data);
+        }
+        main.n_encode += extra[(size_t) i]->n_encode;
+        main.n_decode += extra[(size_t) i]->n_decode;
+        main.n_batchd += extra[(size_t) i]->n_batchd;
+        main.n_prompt += extra[(size_t) i]->n_prompt;
+        whisper_free_state(extra[(size_t) i]);
+    }
+    return ret;
+    WB_CATCH(-1)
+}
+
+#define SEG(state, i) ((state)->result_all[(size_t) (i)])
+int whisper_full_n_segments_from_state(struct whisper_state * state) { return (int) state->result_all.size(); }
+int whisper_full_n_segments(struct whisper_context * ctx) { return (int) ctx->state->result_all.size(); }
+int whisper_full_lang_id_from_state(struct whisper_state * state) { return state->lang_id; }
+int whisper_full_lang_id(struct whisper_context * ctx) { return ctx->state->lang_id; }
+int64_t whisper_full_get_segment_t0_from_state(struct whisper_state * state, int i) { return SEG(state, i).t0; }
+int64_t whisper_full_get_segment_t0(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).t0; }
+int64_t whisper_full_get_segment_t1_from_state(struct whisper_state * state, int i) { return SEG(state, i).t1; }
+int64_t whisper_full_get_segment_t1(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).t1; }
+bool whisper_full_get_segment_speaker_turn_next_from_state(struct whisper_state * state, int i) { return SEG(state, i).speaker_turn_next; }
+bool whisper_full_get_segment_speaker_turn_next(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).speaker_turn_next; }
+const char * whisper_full_get_segment_text_from_state(struct whisper_state * state, int i) { return SEG(state, i).text.c_str(); }
+const char * whisper_full_get_segment_text(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).text.c_str(); }
+int whisper_full_n_tokens_from_state(struct whisper_state * state, int i) { return (int) SEG(state, i).tokens.size(); }
+int whisper_full_n_tokens(struct whisper_context * ctx, int i) { return (int) SEG(ctx->state, i).tokens.size(); }
+const char * whisper_full_get_token_text_from_state(struct whisper_context * ctx, struct whisper_state * state, int i, int j) {
+    return whisper_token_to_str(ctx, SEG(state, i).tokens[(size_t) j].id);
+}
+const char * whisper_full_get_token_text(struct whisper_context * ctx, int i, int j) {
+    return whisper_token_to_str(ctx, SEG(ctx->state, i).tokens[(size_t) j].id);
+}
+whisper_token whisper_full_get_token_id_from_state(struct whisper_state * state, int i, int j) { return SEG(state, i).tokens[(size_t) j].id; }
+whisper_token whisper_full_get_token_id(struct whisper_context * ctx, int i, int j) { return SEG(ctx->state, i).tokens[(size_t) j].id; }
+whisper_token_data whisper_full_get_token_data_from_state(struct whisper_state * state, int i, int j) { return SEG(state, i).tokens[(size_t) j]; }
+whisper_token_data whisper_full_get_token_data(struct whisper_context * ctx, int i, int j) { return SEG(ctx->state, i).tokens[(size_t) j]; }
+float whisper_full_get_token_p_from_state(struct whisper_state * state, int i, int j) { return SEG(state, i).tokens[(size_t) j].p; }
+float whisper_full_get_token_p(struct whisper_context * ctx, int i, int j) { return SEG(ctx->state, i).tokens[(size_t) j].p; }
+float whisper_full_get_segment_no_speech_prob_from_state(struct whisper_state * state, int i) { return SEG(state, i).no_speech_prob; }
+float whisper_full_get_segment_no_speech_prob(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).no_speech_prob; }
+#undef SEG
+
+// ---------------------------------------------------------------------------------------------
+// VAD front end and ggml micro-benchmarks: outside the hot path; present for link completeness
+// ---------------------------------------------------------------------------------------------
+struct whisper_vad_context_params whisper_vad_default_context_params(void) {
+    struct whisper_vad_context_params r;
+    r.n_threads = 4;
+    r.use_gpu = false;
+    r.gpu_device = 0;
+    return r;
+}
+static void vad_unavailable(const char * fn) { log_error("%s: the Silero VAD front end is not part of this library\n", fn); }
+struct whisper_vad_context * whisper_vad_init_from_file_with_params(const char *, struct whisper_vad_context_params) { vad_unavailable(__func__); return nullptr; }
+struct whisper_vad_context * whisper_vad_init_with_params(struct whisper_model_loader *, struct whisper_vad_context_params) { vad_unavailable(__func__); return nullptr; }
+bool whisper_vad_detect_speech(struct whisper_vad_context *, const float *, int) { vad_unavailable(__func__); return false; }
+int whisper_vad_n_probs(struct whisper_vad_context *) { return 0; }
+float * whisper_vad_probs(struct whisper_vad_context *) { return nullptr; }
+struct whisper_vad_segments * whisper_vad_segments_from_probs(struct whisper_vad_context *, struct whisper_vad_params) { vad_unavailable(__func__); return nullptr; }
+struct whisper_vad_segments * whisper_vad_segments_from_samples(struct whisper_vad_context *, struct whisper_vad_params, const float *, int) { vad_unavailable(__func__); return nullptr; }
+int whisper_vad_segments_n_segments(struct whisper_vad_segments *) { return 0; }
+float whisper_vad_segments_get_segment_t0(struct whisper_vad_segments *, int) { return 0.0f; }
+float whisper_vad_segments_get_segment_t1(struct whisper_vad_segments *, int) { return 0.0f; }
+void whisper_vad_free_segments(struct whisper_vad_segments *) {}
+void whisper_vad_free(struct whisper_vad_context *) {}
+int whisper_bench_memcpy(int) { return 0; }
+const char * whisper_bench_memcpy_str(int) { return "not available: use bench.py\n"; }
+int whisper_bench_ggml_mul_mat(int) { return 0; }
+const char * whisper_bench_ggml_mul_mat_str(int) { return "not available: use bench.py\n"; }
+
+// ---------------------------------------------------------------------------------------------
+// whisper_b200.h extensions
+// ---------------------------------------------------------------------------------------------
+int whisper_b200_encode_batch(struct whisper_context * ctx, struct whisper_state ** states, const int * offsets, int n_states) {
+    WB_TRY
+    if (!ctx || !states || !offsets || n_states <= 0) return -1;
+    std::vector<State *> sp(states, states + n_states);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return stage_encode(*ctx, sp.data(), offsets, n_states) ? 0 : -1;
+    WB_CATCH(-1)
+}
+int whisper_b200_decode_batch(struct whisper_context * ctx, struct whisper_state ** states, const whisper_token * tokens, const int * n_past,
+                              int n_states) {
+    WB_TRY
+    if (!ctx || !states || !tokens || !n_past || n_states <= 0) return 1;
+    std::vector<BatchRow> rows;
+    for (int i = 0; i < n_states; ++i) {
+        rows.push_back(BatchRow{states[i], tokens[i], n_past[i], 0, true});
+        states[i]->kv_self.seq_rm(0, n_past[i], -1);
+    }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!stage_decode(*ctx, rows.data(), n_states, false) || !stage_fetch_logits(*ctx, rows.data(), n_states)) return 1;
+    return 0;
+    WB_CATCH(1)
+}
+
+int64_t whisper_b200_get_mel(struct whisper_state * state, float * dst, int64_t cap, int * n_len, int * n_len_org, int * n_mel) {
+    if (!state || !state->ctx) return -1;
+    if (n_len) *n_len = state->n_len;
+    if (n_len_org) *n_len_org = state->n_len_org;
+    if (n_mel) *n_mel = state->n_mel;
+    const int64_t n = (int64_t) state->n_len * state->n_mel;
+    if (dst && cap >= n && n > 0) {
+        std::lock_guard<std::mutex> lk(state->ctx->mu);
+        cudaSetDevice(state->ctx->model.device);
+        if (cudaMemcpy(dst, state->d_mel, (size_t) n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    }
+    return n;
+}
+int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int window, float * dst, int64_t cap) {
+    if (!ctx || !ctx->enc_ws.base || window < 0 || window >= ctx->enc_ws.windows) return -1;
+    const int64_t n = (int64_t) ctx->enc_ws.T * ctx->model.hp.n_audio_state;
+    if (dst && cap >= n) {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        cudaSetDevice(ctx->model.device);
+        if (cudaMemcpy(dst, ctx->enc_ws.enc32 + (size_t) window * n, (size_t) n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    }
+    return n;
+}
+int64_t whisper_b200_get_kv_cross(struct whisper_state * state, uint16_t * dst, int64_t cap) {
+    if (!state || !state->ctx || state->cross_T <= 0) return -1;
+    const auto & hp = state->ctx->model.hp;
+    const int64_t n = (int64_t) hp.n_text_layer * 2 * hp.n_text_head * state->cross_T * 64;
+    if (dst && cap >= n) {
+        std::lock_guard<std::mutex> lk(state->ctx->mu);
+        cudaSetDevice(state->ctx->model.device);
+        if (cudaMemcpy(dst, state->kv_cross, (size_t) n * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    }
+    return n;
+}
+int64_t whisper_b200_get_aheads_qk(struct whisper_state * state, float * dst, int64_t cap) {
+    if (!state || !state->ctx || !state->d_qk) return -1;
+    const int64_t n = (int64_t) state->qk_cap;
+    if (dst && cap >= n) {
+        std::lock_guard<std::mutex> lk(state->ctx->mu);
+        cudaSetDevice(state->ctx->model.device);
+        if (cudaMemcpy(dst, state->d_qk, (size_t) n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    }
+    return n;
+}
+void whisper_b200_get_counters(struct whisper_state * s, int32_t * c, int64_t * us) {
+    if (!s) return;
+    if (c) {
+        c[0] = s->n_sample; c[1] = s->n_encode; c[2] = s->n_decode; c[3] = s->n_batchd; c[4] = s->n_prompt; c[5] = s->n_fail_p; c[6] = s->n_fail_h;
+    }
+    if (us) {
+        us[0] = s->t_sample_us; us[1] = s->t_encode_us; us[2] = s->t_decode_us; us[3] = s->t_batchd_us; us[4] = s->t_prompt_us; us[5] = s->t_mel_us;
+    }
+}
+uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count(); }
+void whisper_b200_device_sync(struct whisper_context * ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->model.device);
+    cudaStreamSynchronize(ctx->stream);
+}
+
+int whisper_b200_test_gemm(const void * a, const void * b, void * c, int m, int n, int k, int lda, int ldb, int ldc, int c_is_f16,
+                           const float * bias, int block_n) {
+    WB_TRY
+    GemmOperand A{}, B{};
+    A.ptr = a; A.rows = m; A.row_stride = lda; A.batch = 1; A.phases = 1;
+    B.ptr = b; B.rows = n; B.row_stride = ldb; B.batch = 1; B.phases = 1;
+    GemmEpilogue e{};
+    e.out = c; e.out_f16 = c_is_f16; e.out_mode = OUT_ROW; e.ldo = ldc; e.batch_div = 1; e.bias = bias;
+    if (!gemm_f16_tc(A, B, m, n, k, 1, e, block_n, 0)) return 1;
+    return cudaGetLastError() == cudaSuccess ? 0 : 2;
+    WB_CATCH(3)
+}
+int whisper_b200_test_mel(struct whisper_context * ctx, const float * d_pcm, int n_samples, float * d_mel) {
+    WB_TRY
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->model.device);
+    static int * d_max = nullptr;
+    if (!d_max && cudaMalloc((void **) &d_max, sizeof(int)) != cudaSuccess) return 1;
+    MelTables tab{ctx->model.mel_sin, ctx->model.mel_cos, ctx->model.mel_hann, ctx->model.mel_filters_t, ctx->model.filters_n_mel};
+    return mel_compute(tab, d_pcm, n_samples, mel_n_len(n_samples), d_mel, d_max, 0) ? 0 : 1;
+    WB_CATCH(3)
+}
+int whisper_b200_test_cross_attn(const void * q, const void * kv, void * out, int n_rows, int n_head, int n_ctx) {
+    WB_TRY
+    static CrossKvRow * d_rows = nullptr;
+    static int cap = 0;
+    if (n_rows > cap) {
+        cudaFree(d_rows);
+        if (cudaMalloc((void **) &d_rows, (size_t) n_rows * sizeof(CrossKvRow)) != cudaSuccess) return 1;
+        cap = n_rows;
+        std::vector<CrossKvRow> h((size_t) n_rows);
+        for (auto & r : h) r = CrossKvRow{(const __half *) kv, nullptr, 0, 0};
+        if (cudaMemcpy(d_rows, h.data(), h.size() * sizeof(CrossKvRow), cudaMemcpyHostToDevice) != cudaSuccess) return 1;
+    }
+    const float scale = (float) pow(64.0, -0.25);
+    return cross_attn_decode((const __half *) q, n_head * 64, d_rows, n_rows, n_head, n_ctx, 0, scale, nullptr, (__half *) out, n_head * 64, 0) ? 0 : 1;
+    WB_CATCH(3)
+}
+
+}  // extern "C"

@@ -1,0 +1,1004 @@
+// F1: the transcription control loop (whisper_full_with_state, wc:6795-7711), restated as a resumable per-state
+// job so that any number of states advance in lock-step: every iteration gathers the decoder rows of all jobs
+// (prompt rows or one row per live decoder), runs ONE batched decoder forward + ONE sampler launch on the
+// device, and lets each job do its host-side bookkeeping.  A single whisper_full_with_state call is a batch of 1.
+//
+// Host work here is integer/bookkeeping only: the state machine of wc:7297-7379, sequence ranking (wc:6567-6613),
+// temperature fallback (wc:7484-7544), segment emission (wc:7569-7676), prompt carry-over.  Token picking at
+// temperature 0 happens in the sampler kernel; temperature > 0 and beam search draw from the device-computed
+// distributions with the same std::mt19937 / std::discrete_distribution sequence as the reference (wc:6476, 6549).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <regex>
+
+#include "engine.h"
+#include "log.h"
+
+namespace wb {
+
+// --------------------------------------------------------------------------------------------
+// suppress mask (the static part of whisper_process_logits, wc:6195-6260)
+// --------------------------------------------------------------------------------------------
+static const char * const k_non_speech_tokens[] = {
+    "\"", "#", "(", ")", "*", "+", "/", ":", ";", "<", "=", ">", "@", "[", "\\", "]", "^", "_", "`", "{", "|", "}", "~",
+    "\xe3\x80\x8c", "\xe3\x80\x8d", "\xe3\x80\x8e", "\xe3\x80\x8f", "<<", ">>", "<<<", ">>>", "--", "---", "-(", "-[", "('", "(\"", "((",
+    "))", "(((", ")))", "[[", "]]", "{{", "}}", "\xe2\x99\xaa\xe2\x99\xaa", "\xe2\x99\xaa\xe2\x99\xaa\xe2\x99\xaa", "\xe2\x99\xa9",
+    "\xe2\x99\xaa", "\xe2\x99\xab", "\xe2\x99\xac", "\xe2\x99\xad", "\xe2\x99\xae", "\xe2\x99\xaf"};
+
+bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
+    const Vocab & vc = ctx.model.vocab;
+    const int V = vc.n_vocab;
+    std::vector<uint8_t> & mk = ctx.suppress_host;
+    mk.assign((size_t) V, 0);
+    auto kill = [&](int id) {
+        if (id >= 0 && id < V) mk[(size_t) id] = 1;
+    };
+    kill(vc.token_not);
+    kill(vc.token_sot);
+    kill(vc.token_nosp);
+    if (!params.tdrz_enable) kill(vc.token_solm);
+    kill(vc.token_translate);
+    kill(vc.token_transcribe);
+    kill(vc.token_prev);
+    for (int i = 0; i < 100; ++i) kill(vc.token_sot + 1 + i);  // whisper_token_lang over the whole language table (wc:6219-6221)
+    if (params.suppress_regex != nullptr) {
+        try {
+            std::regex re(params.suppress_regex);
+            for (const auto & kv : vc.token_to_id)
+                if (std::regex_match(kv.first, re)) kill(kv.second);
+        } catch (const std::regex_error &) {
+            log_error("%s: invalid suppress_regex\n", __func__);
+        }
+    }
+    if (params.suppress_nst) {
+        for (const char * t : k_non_speech_tokens) {
+            const std::string a = t, b = " " + a;
+            auto ia = vc.token_to_id.find(a);
+            if (ia != vc.token_to_id.end()) kill(ia->second);
+            auto ib = vc.token_to_id.find(b);
+            if (ib != vc.token_to_id.end()) kill(ib->second);
+        }
+        auto i1 = vc.token_to_id.find(" -");
+        if (i1 != vc.token_to_id.end()) kill(i1->second);
+        auto i2 = vc.token_to_id.find(" '");
+        if (i2 != vc.token_to_id.end()) kill(i2->second);
+    }
+    WB_CUDA_OK(cudaMemcpyAsync(ctx.d_suppress, mk.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream));
+    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    return true;
+}
+
+static SamplerStatic sampler_static(Context & ctx) {
+    const Vocab & vc = ctx.model.vocab;
+    SamplerStatic s{};
+    s.suppress = ctx.d_suppress;
+    s.n_vocab = vc.n_vocab;
+    s.token_eot = vc.token_eot;
+    s.token_beg = vc.token_beg;
+    auto it = vc.token_to_id.find(" ");
+    s.token_space = it != vc.token_to_id.end() ? it->second : -1;
+    s.token_nosp = vc.token_nosp;
+    return s;
+}
+
+// --------------------------------------------------------------------------------------------
+// host-side sampling from device-computed distributions (wc:6432-6564)
+// --------------------------------------------------------------------------------------------
+static void ts_stats(const Vocab & vc, const std::vector<float> & probs, whisper_token & tid, float & pt, float & ptsum) {
+    double sum_ts = 0.0, max_ts = 0.0;
+    for (int i = vc.token_beg; i < vc.n_vocab; i++) {
+        if (probs[i] == -INFINITY) continue;
+        sum_ts += probs[i];
+        if (max_ts < probs[i]) {
+            max_ts = probs[i];
+            tid = i;
+        }
+    }
+    pt = (float) (max_ts / (sum_ts + 1e-10));
+    ptsum = (float) sum_ts;
+}
+
+static whisper_token_data sample_token_host(const Vocab & vc, Decoder & d) {
+    whisper_token_data r = {0, 0, 0.0f, 0.0f, 0.0f, 0.0f, -1, -1, -1, 0.0f};
+    ts_stats(vc, d.probs, r.tid, r.pt, r.ptsum);
+    std::discrete_distribution<> dist(d.probs.begin(), d.probs.end());
+    r.id = dist(d.rng);
+    r.p = d.probs[r.id];
+    r.plog = d.logprobs[r.id];
+    if (r.id >= vc.token_beg) {
+        r.tid = r.id;
+        r.pt = r.p;
+    }
+    return r;
+}
+
+static std::vector<whisper_token_data> sample_token_topk_host(const Vocab & vc, Decoder & d, int k) {
+    std::vector<whisper_token_data> result;
+    result.reserve(k);
+    whisper_token tid = vc.token_beg;
+    float pt = 0.0f, ptsum = 0.0f;
+    ts_stats(vc, d.probs, tid, pt, ptsum);
+    std::discrete_distribution<> dist(d.probs.begin(), d.probs.end());
+    for (int i = 0; i < k; ++i) {
+        const int id = dist(d.rng);
+        result.push_back({id, tid, d.probs[id], d.logprobs[id], pt, ptsum, -1, -1, -1, 0.0f});
+        if (result[i].id >= vc.token_beg) {
+            result[i].tid = result[i].id;
+            result[i].pt = result[i].p;
+        }
+    }
+    return result;
+}
+
+static whisper_token_data token_from_pick(const SamplerOut & o) {
+    whisper_token_data r = {o.id, o.tid, o.p, o.plog, o.pt, o.ptsum, -1, -1, -1, 0.0f};
+    return r;
+}
+
+// wc:6567-6613
+static void sequence_score(const whisper_full_params & params, Sequence & sq) {
+    if (sq.result_len == 0) return;
+    double result = 0.0;
+    for (int i = 0; i < sq.result_len; ++i) result += sq.tokens[i].plog;
+    sq.sum_logprobs = result;
+    sq.avg_logprobs = result / sq.result_len;
+    double penalty = sq.result_len;
+    if (params.length_penalty > 0.0f) penalty = pow((5.0 + penalty) / 6.0, params.length_penalty);
+    sq.score = result / penalty;
+    const int n = 32;
+    int cnt = 0;
+    double entropy = 0.0;
+    std::map<whisper_token, int> counts;
+    for (int i = std::max(0, sq.result_len - n); i < sq.result_len; ++i) {
+        counts[sq.tokens[i].id]++;
+        cnt++;
+    }
+    for (const auto & kv : counts) {
+        const double p = kv.second / (double) cnt;
+        entropy -= p * log(p);
+    }
+    sq.entropy = entropy;
+}
+
+static bool sequences_equal(const Sequence & a, const Sequence & b) {
+    if (a.tokens.size() != b.tokens.size()) return false;
+    for (int i = (int) a.tokens.size() - 1; i >= 0; i--)
+        if (a.tokens[i].id != b.tokens[i].id) return false;
+    return true;
+}
+
+static const char * token_str(const Vocab & vc, int id) {
+    if (id < 0 || id >= (int) vc.id_to_token.size()) return "";
+    return vc.id_to_token[(size_t) id].c_str();
+}
+
+// --------------------------------------------------------------------------------------------
+// the per-state job
+// --------------------------------------------------------------------------------------------
+struct BeamCandidate {
+    int decoder_idx;
+    int seek_delta;
+    bool has_ts;
+    Sequence sequence;
+};
+
+struct FullJob {
+    enum Phase { WINDOW_BEGIN, TEMP_BEGIN, AFTER_PROMPT, STEP, DONE };
+
+    Context * ctx = nullptr;
+    State * st = nullptr;
+    whisper_full_params params{};
+    const float * samples = nullptr;
+    int n_samples = 0;
+
+    int ret = 0;
+    Phase phase = WINDOW_BEGIN;
+
+    int seek_start = 0, seek_end = 0, seek = 0;
+    std::vector<float> temperatures;
+    int n_decoders = 1;
+    std::vector<whisper_token> prompt_init, prompt, prompt_tokens_buf;
+
+    int it = 0, n_decoders_cur = 1, best_decoder_id = 0, i = 0, n_max = 0;
+    float t_cur = 0.0f;
+    bool host_sampling = false;
+
+    std::vector<std::vector<BeamCandidate>> bc_per_dec;
+    std::vector<BeamCandidate> beam_candidates;
+
+    // contribution to the current device iteration
+    std::vector<BatchRow> rows;
+    std::vector<SamplerRow> srows;
+    std::vector<Decoder *> sdecs;
+
+    static constexpr int delta_min = 10;
+
+    whisper_context * wctx() const { return static_cast<whisper_context *>(ctx); }
+    whisper_state * wstate() const { return static_cast<whisper_state *>(st); }
+    const Vocab & vocab() const { return ctx->model.vocab; }
+
+    void finish(int r) {
+        ret = r;
+        phase = DONE;
+        rows.clear();
+        srows.clear();
+        sdecs.clear();
+    }
+
+    bool init();
+    bool window_begin();   // true: this job needs its window encoded at `seek`
+    void after_encode();
+    void temp_begin();
+    void after_device();
+    void after_prompt();
+    void step();
+    void finish_temperature();
+    void emit_results();
+    SamplerRow sampler_row(const Decoder & d, int logits_row, bool want_nosp) const;
+    void queue_step_rows();
+};
+
+// everything of wc:6801-6984 after the mel computation
+bool FullJob::init() {
+    const Vocab & vc = vocab();
+    st->result_all.clear();
+
+    // language detection (wc:6815-6830)
+    if (params.language == nullptr || strlen(params.language) == 0 || strcmp(params.language, "auto") == 0 || params.detect_language) {
+        std::vector<float> probs(100, 0.0f);
+        const int lid = lang_auto_detect(ctx, st, 0, probs.data());
+        if (lid < 0) {
+            log_error("%s: failed to auto-detect language\n", __func__);
+            finish(-3);
+            return false;
+        }
+        st->lang_id = lid;
+        params.language = g_langs[lid].code;
+        log_msg(GGML_LOG_LEVEL_INFO, "%s: auto-detected language: %s (p = %f)\n", __func__, params.language, probs[lid]);
+        if (params.detect_language) {
+            finish(0);
+            return false;
+        }
+    }
+    if (params.token_timestamps) {
+        st->t_beg = 0;
+        st->t_last = 0;
+        st->tid_last = 0;
+    }
+    seek_start = params.offset_ms / 10;
+    seek_end = params.duration_ms == 0 ? st->n_len_org : seek_start + params.duration_ms / 10;
+    if (seek_end < seek_start + delta_min) {
+        log_msg(GGML_LOG_LEVEL_WARN, "%s: input is too short - %d ms < 100 ms. consider padding the input audio with silence\n", __func__,
+                (seek_end - seek_start) * 10);
+        finish(0);
+        return false;
+    }
+    temperatures.clear();
+    if (params.temperature_inc > 0.0f) {
+        for (float t = params.temperature; t < 1.0f + 1e-6f; t += params.temperature_inc) temperatures.push_back(t);
+    } else {
+        temperatures.push_back(params.temperature);
+    }
+    n_decoders = 1;
+    switch (params.strategy) {
+        case WHISPER_SAMPLING_GREEDY: n_decoders = params.greedy.best_of; break;
+        case WHISPER_SAMPLING_BEAM_SEARCH: n_decoders = std::max(params.greedy.best_of, params.beam_search.beam_size); break;
+    }
+    n_decoders = std::max(1, n_decoders);
+    if (n_decoders > MAX_DECODERS) {
+        log_error("%s: too many decoders requested (%d), max = %d\n", __func__, n_decoders, MAX_DECODERS);
+        finish(-4);
+        return false;
+    }
+    for (int j = 1; j < n_decoders; j++) st->decoders[j].rng = std::mt19937(j);  // wc:6897
+
+    auto & prompt_past = st->prompt_past;
+    if (params.no_context) prompt_past.clear();
+    // initial prompt (wc:6907-6931)
+    if (!params.prompt_tokens && params.initial_prompt) {
+        prompt_tokens_buf.resize(1024);
+        int n_needed = whisper_tokenize(wctx(), params.initial_prompt, prompt_tokens_buf.data(), (int) prompt_tokens_buf.size());
+        if (n_needed < 0) {
+            prompt_tokens_buf.resize((size_t) -n_needed);
+            n_needed = whisper_tokenize(wctx(), params.initial_prompt, prompt_tokens_buf.data(), (int) prompt_tokens_buf.size());
+        }
+        prompt_tokens_buf.resize((size_t) std::max(0, n_needed));
+        params.prompt_tokens = prompt_tokens_buf.data();
+        params.prompt_n_tokens = (int) prompt_tokens_buf.size();
+    }
+    if (params.prompt_tokens && params.prompt_n_tokens > 0) {
+        for (int k = 0; k < params.prompt_n_tokens; k++) prompt_past.push_back(params.prompt_tokens[k]);
+        std::rotate(prompt_past.begin(), prompt_past.end() - params.prompt_n_tokens, prompt_past.end());
+    }
+    if (params.audio_ctx > ctx->model.hp.n_audio_ctx) {
+        log_error("%s: audio_ctx is larger than the maximum allowed (%d > %d)\n", __func__, params.audio_ctx, ctx->model.hp.n_audio_ctx);
+        finish(-5);
+        return false;
+    }
+    st->exp_n_audio_ctx = params.audio_ctx;
+
+    prompt_init = {vc.token_sot};
+    if (vc.is_multilingual()) {
+        const int lid = lang_id(params.language);
+        if (lid < 0) log_error("%s: unknown language '%s'\n", "whisper_lang_id", params.language);
+        st->lang_id = lid;
+        prompt_init.push_back(vc.token_sot + 1 + lid);
+        prompt_init.push_back(params.translate ? vc.token_translate : vc.token_transcribe);
+    }
+    {
+        const bool is_distil = ctx->model.hp.n_text_layer == 2 && ctx->model.hp.n_vocab != 51866;
+        if (is_distil && !params.no_timestamps) {
+            log_msg(GGML_LOG_LEVEL_WARN, "%s: using first release distilled models - forcing no_timestamps\n", __func__);
+            params.no_timestamps = true;
+        }
+    }
+    if (params.no_timestamps) prompt_init.push_back(vc.token_not);
+
+    seek = seek_start;
+    prompt.reserve((size_t) ctx->model.hp.n_text_ctx);
+    bc_per_dec.assign((size_t) n_decoders, {});
+    n_max = ctx->model.hp.n_text_ctx / 2 - 4;
+    phase = WINDOW_BEGIN;
+    return true;
+}
+
+// head of the main loop (wc:6986-7004)
+bool FullJob::window_begin() {
+    if (params.progress_callback) {
+        const int progress_cur = (100 * (seek - seek_start)) / (seek_end - seek_start);
+        params.progress_callback(wctx(), wstate(), progress_cur, params.progress_callback_user_data);
+    }
+    if (seek + delta_min >= seek_end) {
+        finish(0);
+        return false;
+    }
+    if (params.encoder_begin_callback) {
+        if (params.encoder_begin_callback(wctx(), wstate(), params.encoder_begin_callback_user_data) == false) {
+            log_error("%s: encoder_begin_callback returned false - aborting\n", __func__);
+            finish(0);
+            return false;
+        }
+    }
+    return true;
+}
+
+void FullJob::after_encode() {
+    if (params.abort_callback && params.abort_callback(params.abort_callback_user_data)) {  // wc:2471
+        log_error("%s: failed to encode\n", __func__);
+        finish(-6);
+        return;
+    }
+    if (seek > seek_start && seek + 500 >= seek_end) st->prompt_past.clear();  // wc:7014-7016
+    best_decoder_id = 0;
+    it = 0;
+    phase = TEMP_BEGIN;
+}
+
+SamplerRow FullJob::sampler_row(const Decoder & d, int logits_row, bool want_nosp) const {
+    const Vocab & vc = vocab();
+    const auto & tk = d.sequence.tokens;
+    SamplerRow r{};
+    r.logits_row = logits_row;
+    r.temperature = t_cur;
+    r.is_initial = tk.empty() ? 1 : 0;
+    r.suppress_blank = params.suppress_blank ? 1 : 0;
+    r.no_timestamps = params.no_timestamps ? 1 : 0;
+    r.last_was_ts = (!tk.empty() && tk.back().id >= vc.token_beg) ? 1 : 0;
+    r.penult_was_ts = (tk.size() < 2 || tk[tk.size() - 2].id >= vc.token_beg) ? 1 : 0;
+    r.max_initial_tid = vc.n_vocab;
+    if (tk.empty() && params.max_initial_ts > 0.0f) {  // wc:6285-6292
+        const float precision = float(WHISPER_CHUNK_SIZE) / ctx->model.hp.n_audio_ctx;
+        const int tid0 = (int) std::round(params.max_initial_ts / precision);
+        r.max_initial_tid = vc.token_beg + tid0 + 1;
+    }
+    r.has_ts = d.has_ts ? 1 : 0;
+    r.tid0 = d.seek_delta / 2;
+    r.want_nosp = want_nosp ? 1 : 0;
+    r.work_slot = logits_row;
+    return r;
+}
+
+// start of one temperature pass (wc:7020-7155): decoder reset, prompt assembly, KV reset, prompt rows
+void FullJob::temp_begin() {
+    const Vocab & vc = vocab();
+    const auto & hp = ctx->model.hp;
+    t_cur = temperatures[(size_t) it];
+    n_decoders_cur = 1;
+    switch (params.strategy) {
+        case WHISPER_SAMPLING_GREEDY:
+            if (t_cur > 0.0f) n_decoders_cur = params.greedy.best_of;
+            break;
+        case WHISPER_SAMPLING_BEAM_SEARCH:
+            n_decoders_cur = t_cur > 0.0f ? params.greedy.best_of : params.beam_search.beam_size;
+            break;
+    }
+    n_decoders_cur = std::max(1, n_decoders_cur);
+    host_sampling = params.strategy == WHISPER_SAMPLING_BEAM_SEARCH || !(t_cur < 1e-6f);
+
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        Decoder & d = st->decoders[j];
+        d.sequence.tokens.clear();
+        d.sequence.result_len = 0;
+        d.sequence.sum_logprobs_all = 0.0;
+        d.sequence.sum_logprobs = -INFINITY;
+        d.sequence.avg_logprobs = -INFINITY;
+        d.sequence.entropy = 0.0;
+        d.sequence.score = -INFINITY;
+        d.seek_delta = 100 * WHISPER_CHUNK_SIZE;
+        d.failed = false;
+        d.completed = false;
+        d.has_ts = false;
+        d.want_dists = host_sampling;
+    }
+    prompt.clear();
+    auto & prompt_past = st->prompt_past;
+    if (!prompt_past.empty() && t_cur < 0.5f && params.n_max_text_ctx > 0) {
+        const int n_take = std::min(std::min(params.n_max_text_ctx, hp.n_text_ctx / 2), int(prompt_past.size()));
+        prompt = {vc.token_prev};
+        prompt.insert(prompt.begin() + 1, prompt_past.end() - n_take, prompt_past.end());
+    }
+    prompt.insert(prompt.end(), prompt_init.begin(), prompt_init.end());
+
+    if (st->kv_self_n_dec < n_decoders_cur) {  // wc:7095-7113
+        const int factor = n_decoders_cur > 1 ? n_decoders_cur + 2 : 1;
+        if (!kv_self_alloc(*st, (int) pad_to(hp.n_text_ctx, 256) * factor)) {
+            log_error("%s: whisper_kv_cache_init() failed for self-attention cache\n", __func__);
+            finish(-7);
+            return;
+        }
+        st->kv_self_n_dec = n_decoders_cur;
+    }
+    st->kv_self.clear();
+
+    rows.clear();
+    srows.clear();
+    sdecs.clear();
+    for (int k = 0; k < (int) prompt.size(); ++k) rows.push_back(BatchRow{st, prompt[(size_t) k], k, 0, k == (int) prompt.size() - 1});
+    st->decoders[0].i_batch = (int) prompt.size() - 1;
+    srows.push_back(sampler_row(st->decoders[0], 0, true));
+    sdecs.push_back(&st->decoders[0]);
+    phase = AFTER_PROMPT;
+}
+
+// the device has run this job's rows: decoder forward + sampler
+void FullJob::after_device() {
+    if (params.abort_callback && params.abort_callback(params.abort_callback_user_data)) {  // wc:2993
+        log_error("%s: failed to decode\n", __func__);
+        finish(phase == AFTER_PROMPT ? -8 : -9);
+        return;
+    }
+    if (phase == AFTER_PROMPT) {
+        after_prompt();
+    } else if (phase == STEP) {
+        ++i;
+        if (i < n_max) step();
+        else finish_temperature();
+    }
+}
+
+void FullJob::after_prompt() {
+    st->no_speech_prob = st->decoders[0].picked.nosp_prob;  // wc:7126-7134
+    for (int j = 1; j < n_decoders_cur; ++j) {              // wc:7143-7151
+        Decoder & d = st->decoders[j];
+        st->kv_self.seq_cp(0, j, -1, -1);
+        d.picked = st->decoders[0].picked;
+        if (host_sampling) {
+            d.probs = st->decoders[0].probs;
+            d.logits = st->decoders[0].logits;
+            d.logprobs = st->decoders[0].logprobs;
+        }
+    }
+    i = 0;
+    phase = STEP;
+    step();
+}
+
+// one iteration of the token loop, host part (wc:7157-7398): pick tokens, beam bookkeeping, decoder state machine
+void FullJob::step() {
+    const Vocab & vc = vocab();
+    const int64_t t_start = time_us();
+    const bool beam = params.strategy == WHISPER_SAMPLING_BEAM_SEARCH;
+    if (beam)
+        for (auto & bc : bc_per_dec) bc.clear();
+
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        Decoder & d = st->decoders[j];
+        if (d.completed || d.failed) continue;
+        if (!beam) {
+            if (t_cur < 1e-6f) d.sequence.tokens.push_back(token_from_pick(d.picked));
+            else d.sequence.tokens.push_back(sample_token_host(vc, d));
+            d.sequence.sum_logprobs_all += d.sequence.tokens.back().plog;
+        } else {
+            const auto tokens_new = sample_token_topk_host(vc, d, params.beam_search.beam_size);
+            for (const auto & token : tokens_new) {
+                bc_per_dec[(size_t) j].push_back({j, d.seek_delta, d.has_ts, d.sequence});
+                bc_per_dec[(size_t) j].back().sequence.tokens.push_back(token);
+                bc_per_dec[(size_t) j].back().sequence.sum_logprobs_all += token.plog;
+            }
+        }
+    }
+    beam_candidates.clear();
+    for (const auto & bc : bc_per_dec) {
+        beam_candidates.insert(beam_candidates.end(), bc.begin(), bc.end());
+        if (!bc.empty()) st->n_sample += 1;
+    }
+    if (beam) {  // wc:7239-7291
+        std::sort(beam_candidates.begin(), beam_candidates.end(), [](const BeamCandidate & a, const BeamCandidate & b) {
+            if (a.sequence.sum_logprobs_all != b.sequence.sum_logprobs_all) return a.sequence.sum_logprobs_all > b.sequence.sum_logprobs_all;
+            return a.decoder_idx < b.decoder_idx;
+        });
+        uint32_t cur_c = 0;
+        for (int j = 0; j < n_decoders_cur; ++j) {
+            Decoder & d = st->decoders[j];
+            if (d.completed || d.failed) continue;
+            if (cur_c >= beam_candidates.size()) cur_c = 0;
+            auto & cur = beam_candidates[cur_c++];
+            while (beam_candidates.size() > cur_c && sequences_equal(beam_candidates[cur_c].sequence, cur.sequence) && i > 0) ++cur_c;
+            d.seek_delta = cur.seek_delta;
+            d.has_ts = cur.has_ts;
+            d.sequence = cur.sequence;
+            st->kv_self.seq_cp(cur.decoder_idx, MAX_DECODERS + j, -1, -1);
+        }
+        for (int j = 0; j < n_decoders_cur; ++j) {
+            Decoder & d = st->decoders[j];
+            if (d.completed || d.failed) continue;
+            st->kv_self.seq_rm(j, -1, -1);
+            st->kv_self.seq_cp(MAX_DECODERS + j, j, -1, -1);
+            st->kv_self.seq_rm(MAX_DECODERS + j, -1, -1);
+        }
+    }
+
+    // decoder state machine (wc:7297-7379)
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        Decoder & d = st->decoders[j];
+        if (d.completed || d.failed) continue;
+        auto & has_ts = d.has_ts;
+        auto & failed = d.failed;
+        auto & completed = d.completed;
+        auto & seek_delta = d.seek_delta;
+        auto & result_len = d.sequence.result_len;
+        {
+            const auto & token = d.sequence.tokens.back();
+            if (token.id > vc.token_beg) {
+                const int seek_delta_new = 2 * (token.id - vc.token_beg);
+                if (has_ts && seek_delta > seek_delta_new && result_len < i) {
+                    failed = true;
+                    continue;
+                }
+                seek_delta = seek_delta_new;
+                result_len = i + 1;
+                has_ts = true;
+            }
+            if (token.id == vc.token_eot || (params.max_tokens > 0 && i >= params.max_tokens) ||
+                (has_ts && seek + seek_delta + delta_min >= seek_end)) {
+                if (result_len == 0 && !params.no_timestamps) {
+                    if (seek + seek_delta + delta_min >= seek_end) {
+                        result_len = i + 1;
+                    } else {
+                        failed = true;
+                        continue;
+                    }
+                }
+                if (params.single_segment || params.no_timestamps) {
+                    result_len = i + 1;
+                    seek_delta = 100 * WHISPER_CHUNK_SIZE;
+                }
+                completed = true;
+                continue;
+            }
+            if (ctx->model.n_loaded == 0) {  // header-only test models (wc:7364-7369)
+                seek_delta = 100 * WHISPER_CHUNK_SIZE;
+                completed = true;
+                continue;
+            }
+        }
+        if (i == n_max - 1 && (result_len == 0 || seek_delta < 100 * WHISPER_CHUNK_SIZE / 2)) {
+            failed = true;
+            continue;
+        }
+    }
+    bool completed_all = true;
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        const Decoder & d = st->decoders[j];
+        if (d.completed || d.failed) continue;
+        completed_all = false;
+    }
+    st->t_sample_us += time_us() - t_start;
+    if (completed_all) {
+        finish_temperature();
+        return;
+    }
+    queue_step_rows();
+}
+
+// one row per live decoder for the next decoder forward (wc:7403-7427) + the matching sampler rows
+void FullJob::queue_step_rows() {
+    rows.clear();
+    srows.clear();
+    sdecs.clear();
+    const int n_past = (int) prompt.size() + i;
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        Decoder & d = st->decoders[j];
+        if (d.failed || d.completed) continue;
+        d.i_batch = (int) rows.size();
+        rows.push_back(BatchRow{st, d.sequence.tokens.back().id, n_past, j, true});
+        srows.push_back(sampler_row(d, 0, false));
+        sdecs.push_back(&d);
+    }
+    phase = STEP;
+}
+
+// rank, decide on fallback (wc:7483-7544), then either restart at the next temperature or emit
+void FullJob::finish_temperature() {
+    rows.clear();
+    srows.clear();
+    sdecs.clear();
+    double best_score = -INFINITY;
+    for (int j = 0; j < n_decoders_cur; ++j) {
+        Decoder & d = st->decoders[j];
+        if (d.failed) continue;
+        d.sequence.tokens.resize((size_t) d.sequence.result_len);
+        sequence_score(params, d.sequence);
+        if (d.sequence.result_len > 32 && d.sequence.entropy < params.entropy_thold) {
+            d.failed = true;
+            st->n_fail_h++;
+            continue;
+        }
+        if (best_score < d.sequence.score) {
+            best_score = d.sequence.score;
+            best_decoder_id = j;
+        }
+    }
+    bool success = true;
+    if (it != (int) temperatures.size() - 1) {
+        const Decoder & d = st->decoders[best_decoder_id];
+        if (d.failed || (d.sequence.avg_logprobs < params.logprob_thold && st->no_speech_prob < params.no_speech_thold)) {
+            success = false;
+            st->n_fail_p++;
+        }
+    }
+    if (!success) {
+        ++it;
+        phase = TEMP_BEGIN;
+        return;
+    }
+    emit_results();
+}
+
+// --------------------------------------------------------------------------------------------
+// X1/X2: DTW token timestamps for the segments of one window (wc:8772-8933)
+// --------------------------------------------------------------------------------------------
+static bool dtw_token_timestamps(Context * ctx, State * st, const whisper_full_params & params, int i_segment, size_t n_segments, int seek,
+                                 int n_frames, int medfilt_width) {
+    const Vocab & vc = ctx->model.vocab;
+    const int T = st->cross_T;
+    std::vector<whisper_token> tokens = {vc.token_sot};
+    if (vc.is_multilingual()) {
+        const int lid = lang_id(params.language);
+        st->lang_id = lid;
+        tokens.push_back(vc.token_sot + 1 + lid);
+    }
+    const int sot_len = (int) tokens.size();
+    tokens.push_back(vc.token_not);
+    for (size_t s = (size_t) i_segment; s < (size_t) i_segment + n_segments; ++s)
+        for (auto & t : st->result_all[s].tokens)
+            if (t.id < vc.token_eot) tokens.push_back(t.id);
+    tokens.push_back(vc.token_eot);
+
+    st->kv_self.clear();
+    const int n_tok = (int) tokens.size();
+    std::vector<BatchRow> rows;
+    for (int k = 0; k < n_tok; ++k) rows.push_back(BatchRow{st, tokens[(size_t) k], k, 0, false});
+    st->kv_self.seq_rm(0, 0, -1);
+    if (!stage_decode(*ctx, rows.data(), n_tok, true)) {
+        log_error("%s: decoder failed while capturing alignment heads\n", __func__);
+        return false;
+    }
+    const int n_audio = n_frames / 2;
+    const int N = n_tok - sot_len - 1;  // rows kept: <|notimestamps|> + text tokens (wc:8882)
+    if (n_audio <= medfilt_width || N <= 0 || ctx->n_aheads <= 0) {
+        WB_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+        return true;  // the reference asserts here (wc:8742); nothing sensible to align
+    }
+    const int H = ctx->n_aheads;
+    float *d_nrm = nullptr, *d_cost = nullptr, *d_diag = nullptr;
+    int8_t * d_trace = nullptr;
+    int * d_path = nullptr;
+    const size_t cap = (size_t) N + n_audio;
+    bool ok = cudaMalloc((void **) &d_nrm, (size_t) H * n_tok * n_audio * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_cost, (size_t) n_tok * n_audio * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_diag, (size_t) 3 * (N + 1) * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_trace, (size_t) (N + 1) * (n_audio + 1)) == cudaSuccess &&
+              cudaMalloc((void **) &d_path, (2 * cap + 1) * 4) == cudaSuccess;
+    std::vector<int> path(2 * cap + 1);
+    if (ok) ok = dtw_cost(st->d_qk, H, n_tok, T, n_audio, medfilt_width, d_nrm, d_cost, ctx->stream);
+    if (ok) ok = dtw_path(d_cost + (size_t) sot_len * n_audio, N, n_audio, d_diag, d_trace, d_path, d_path + 2 * cap, ctx->stream);
+    if (ok) ok = cudaMemcpyAsync(path.data(), d_path, (2 * cap + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess;
+    if (ok) ok = cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+    cudaFree(d_nrm);
+    cudaFree(d_cost);
+    cudaFree(d_diag);
+    cudaFree(d_trace);
+    cudaFree(d_path);
+    if (!ok) {
+        log_error("%s: DTW kernels failed\n", __func__);
+        return false;
+    }
+    const int len = path[2 * cap];
+    const int * pi = path.data() + (cap - (size_t) len);        // text index row
+    const int * pj = path.data() + cap + (cap - (size_t) len);  // time index row
+    // place timestamps (wc:8894-8920)
+    int32_t last_v = 0;
+    auto seg_i = st->result_all.begin() + i_segment;
+    auto tok_i = seg_i->tokens.begin();
+    const auto seg_end = st->result_all.begin() + i_segment + (long) n_segments;
+    for (int k = 0; k < len; ++k) {
+        const int32_t v = pi[k];
+        if (v != last_v) {
+            const int64_t timestamp = (int64_t) pj[k] * 2 + seek;
+            last_v = v;
+            while (seg_i != seg_end && !(tok_i->id < vc.token_eot)) {
+                ++tok_i;
+                if (tok_i == seg_i->tokens.end()) {
+                    ++seg_i;
+                    if (seg_i == seg_end) break;
+                    tok_i = seg_i->tokens.begin();
+                }
+            }
+            if (seg_i == seg_end) break;
+            tok_i->t_dtw = timestamp;
+            ++tok_i;
+            if (tok_i == seg_i->tokens.end()) {
+                ++seg_i;
+                if (seg_i == seg_end) break;
+                tok_i = seg_i->tokens.begin();
+            }
+        }
+    }
+    return true;
+}
+
+// segment emission and window advance (wc:7546-7707)
+void FullJob::emit_results() {
+    const Vocab & vc = vocab();
+    auto & result_all = st->result_all;
+    const Decoder & best = st->decoders[best_decoder_id];
+    int seek_delta = best.seek_delta;
+    const int result_len = best.sequence.result_len;
+    const auto & tokens_cur = best.sequence.tokens;
+    const size_t n_segments_before = result_all.size();
+    const bool is_no_speech = (st->no_speech_prob > params.no_speech_thold && best.sequence.avg_logprobs < params.logprob_thold);
+
+    auto & prompt_past = st->prompt_past;
+    prompt_past.clear();
+    if (prompt.front() == vc.token_prev) prompt_past.insert(prompt_past.end(), prompt.begin() + 1, prompt.end() - (long) prompt_init.size());
+    for (int k = 0; k < result_len && !is_no_speech; ++k) prompt_past.push_back(tokens_cur[(size_t) k].id);
+
+    auto notify = [&](int n_new) {
+        if (params.new_segment_callback && !ctx->params.dtw_token_timestamps)
+            params.new_segment_callback(wctx(), wstate(), n_new, params.new_segment_callback_user_data);
+    };
+
+    if (!tokens_cur.empty() && ctx->model.n_loaded > 0 && !is_no_speech) {
+        int i0 = 0;
+        int64_t t0 = seek + 2 * (tokens_cur.front().tid - vc.token_beg);
+        std::string text;
+        bool speaker_turn_next = false;
+        for (int k = 0; k < (int) tokens_cur.size(); k++) {
+            if (params.print_special || tokens_cur[(size_t) k].id < vc.token_eot) text += token_str(vc, tokens_cur[(size_t) k].id);
+            if (params.tdrz_enable && tokens_cur[(size_t) k].id == vc.token_solm) speaker_turn_next = true;
+            if (tokens_cur[(size_t) k].id > vc.token_beg && !params.single_segment) {
+                const int64_t t1 = seek + 2 * (tokens_cur[(size_t) k].tid - vc.token_beg);
+                if (!text.empty()) {
+                    if (params.print_realtime) {
+                        printf("%s", text.c_str());
+                        fflush(stdout);
+                    }
+                    result_all.push_back({t0, t1, text, st->no_speech_prob, {}, speaker_turn_next});
+                    for (int j = i0; j <= k; j++) result_all.back().tokens.push_back(tokens_cur[(size_t) j]);
+                    notify(1);
+                }
+                text = "";
+                while (k < (int) tokens_cur.size() && tokens_cur[(size_t) k].id > vc.token_beg) k++;
+                k--;
+                t0 = t1;
+                i0 = k + 1;
+                speaker_turn_next = false;
+            }
+        }
+        if (!text.empty()) {
+            const int64_t t1 = seek + seek_delta;
+            if (params.print_realtime) {
+                printf("%s", text.c_str());
+                fflush(stdout);
+            }
+            result_all.push_back({t0, t1, text, st->no_speech_prob, {}, speaker_turn_next});
+            for (int j = i0; j < (int) tokens_cur.size(); j++) result_all.back().tokens.push_back(tokens_cur[(size_t) j]);
+            notify(1);
+        }
+    }
+    {   // DTW (wc:7680-7692)
+        const int n_segments = (int) (result_all.size() - n_segments_before);
+        if (ctx->params.dtw_token_timestamps && n_segments) {
+            const int n_frames = std::min(std::min(WHISPER_CHUNK_SIZE * 100, seek_delta), seek_end - seek);
+            dtw_token_timestamps(ctx, st, params, (int) result_all.size() - n_segments, (size_t) n_segments, seek, n_frames, 7);
+            if (params.new_segment_callback) {
+                for (int seg = (int) result_all.size() - n_segments; seg < n_segments; seg++)
+                    params.new_segment_callback(wctx(), wstate(), seg, params.new_segment_callback_user_data);
+            }
+        }
+    }
+    const bool single_timestamp_ending = tokens_cur.size() > 1 && tokens_cur[tokens_cur.size() - 2].id < vc.token_beg &&
+                                         tokens_cur[tokens_cur.size() - 1].id > vc.token_beg;
+    if (single_timestamp_ending) seek_delta = std::min(seek_end - seek, WHISPER_CHUNK_SIZE * 100);
+    seek += seek_delta;
+    phase = WINDOW_BEGIN;
+}
+
+// --------------------------------------------------------------------------------------------
+// F4: language auto-detection (wc:4037-4110): encode at the offset, decode [sot], softmax over the language logits
+// --------------------------------------------------------------------------------------------
+int lang_auto_detect(Context * ctx, State * st, int offset_ms, float * lang_probs) {
+    const Vocab & vc = ctx->model.vocab;
+    const int seek = offset_ms / 10;
+    if (seek < 0) {
+        log_error("%s: offset %dms is before the start of the audio\n", __func__, offset_ms);
+        return -1;
+    }
+    if (seek >= st->n_len_org) {
+        log_error("%s: offset %dms is past the end of the audio (%dms)\n", __func__, offset_ms, st->n_len_org * 10);
+        return -2;
+    }
+    State * sp = st;
+    if (!stage_encode(*ctx, &sp, &seek, 1)) {
+        log_error("%s: failed to encode\n", __func__);
+        return -6;
+    }
+    BatchRow row{st, vc.token_sot, 0, 0, true};
+    st->kv_self.seq_rm(0, 0, -1);
+    if (!stage_decode(*ctx, &row, 1, false) || !stage_fetch_logits(*ctx, &row, 1)) {
+        log_error("%s: failed to decode\n", __func__);
+        return -7;
+    }
+    // the reference walks its language map in key (code) order before sorting by logit
+    std::vector<int> order(100);
+    for (int i = 0; i < 100; ++i) order[(size_t) i] = i;
+    std::sort(order.begin(), order.end(), [](int a, int b) { return strcmp(g_langs[a].code, g_langs[b].code) < 0; });
+    std::vector<std::pair<double, int>> li;
+    for (int id : order) {
+        const int tok = vc.token_sot + 1 + id;
+        if (tok >= vc.n_vocab) continue;
+        li.emplace_back((double) st->logits[(size_t) tok], id);
+    }
+    std::sort(li.begin(), li.end(), [](const std::pair<double, int> & a, const std::pair<double, int> & b) { return a.first > b.first; });
+    const double mx = li[0].first;
+    double sum = 0.0;
+    for (auto & kv : li) {
+        kv.first = exp(kv.first - mx);
+        sum += kv.first;
+    }
+    for (auto & kv : li) kv.first /= sum;
+    if (lang_probs)
+        for (const auto & kv : li) lang_probs[kv.second] = (float) kv.first;
+    return li[0].second;
+}
+
+// --------------------------------------------------------------------------------------------
+// the lock-step driver
+// --------------------------------------------------------------------------------------------
+int full_with_states(Context * ctx, State * const * states, int n_states, const whisper_full_params * params_arr, bool params_per_state,
+                     const float * const * samples, const int * n_samples) {
+    const whisper_full_params & params_in = params_arr[0];  // suppress rules / strategy are shared by the batch
+    if (cudaSetDevice(ctx->model.device) != cudaSuccess) return -6;
+    std::vector<FullJob> jobs((size_t) n_states);
+    if (!build_suppress_mask(*ctx, params_in)) return -6;
+    const SamplerStatic sst = sampler_static(*ctx);
+
+    for (int k = 0; k < n_states; ++k) {
+        FullJob & j = jobs[(size_t) k];
+        j.ctx = ctx;
+        j.st = states[k];
+        j.params = params_per_state ? params_arr[k] : params_in;
+        j.samples = samples ? samples[k] : nullptr;
+        j.n_samples = n_samples ? n_samples[k] : 0;
+        j.st->result_all.clear();
+        if (j.n_samples > 0) {  // wc:6806-6812
+            if (!stage_pcm_to_mel(*j.st, j.samples, j.n_samples)) {
+                log_error("%s: failed to compute log mel spectrogram\n", __func__);
+                j.finish(-2);
+                continue;
+            }
+        }
+        j.init();
+    }
+
+    std::vector<State *> enc_states;
+    std::vector<int> enc_offsets;
+    std::vector<FullJob *> enc_jobs;
+    std::vector<BatchRow> rows;
+    std::vector<SamplerRow> srows;
+    std::vector<Decoder *> sdecs;
+    std::vector<FullJob *> dev_jobs;
+
+    while (true) {
+        // ---- windows that need their encoder pass
+        enc_states.clear();
+        enc_offsets.clear();
+        enc_jobs.clear();
+        for (auto & j : jobs) {
+            if (j.phase != FullJob::WINDOW_BEGIN) continue;
+            if (j.window_begin()) {
+                enc_states.push_back(j.st);
+                enc_offsets.push_back(j.seek);
+                enc_jobs.push_back(&j);
+            }
+        }
+        if (!enc_jobs.empty()) {
+            if (!stage_encode(*ctx, enc_states.data(), enc_offsets.data(), (int) enc_jobs.size())) {
+                log_error("%s: failed to encode\n", __func__);
+                for (auto * j : enc_jobs) j->finish(-6);
+            } else {
+                for (auto * j : enc_jobs) j->after_encode();
+            }
+        }
+        // ---- gather the decoder rows of every live job
+        rows.clear();
+        srows.clear();
+        sdecs.clear();
+        dev_jobs.clear();
+        bool any_live = false, any_dists = false;
+        for (auto & j : jobs) {
+            if (j.phase == FullJob::DONE) continue;
+            any_live = true;
+            if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
+            if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
+            if (j.rows.empty()) continue;
+            // flagged rows of this job map to consecutive logits rows
+            int flagged = 0;
+            for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
+            const int base = (int) srows.size();
+            if (flagged != (int) j.srows.size()) {
+                log_error("%s: internal error: %d flagged rows vs %zu sampler rows\n", __func__, flagged, j.srows.size());
+                j.finish(-9);
+                continue;
+            }
+            rows.insert(rows.end(), j.rows.begin(), j.rows.end());
+            for (size_t q = 0; q < j.srows.size(); ++q) {
+                SamplerRow sr = j.srows[q];
+                sr.logits_row = base + (int) q;
+                sr.work_slot = base + (int) q;
+                srows.push_back(sr);
+                sdecs.push_back(j.sdecs[q]);
+                any_dists = any_dists || j.sdecs[q]->want_dists;
+            }
+            dev_jobs.push_back(&j);
+        }
+        if (!any_live) break;
+        if (dev_jobs.empty()) continue;
+
+        bool ok = stage_decode(*ctx, rows.data(), (int) rows.size(), false);
+        if (ok && params_in.logits_filter_callback) {
+            // the callback sees host logits between the static suppressions and the timestamp rules (wc:6226-6228):
+            // not supported on the device sampler path
+            static bool warned = false;
+            if (!warned) log_msg(GGML_LOG_LEVEL_WARN, "%s: logits_filter_callback is ignored by the device sampler\n", __func__);
+            warned = true;
+        }
+        ok = ok && stage_sample(*ctx, sst, srows.data(), (int) srows.size(), any_dists, sdecs.data());
+        if (!ok) {
+            log_error("%s: failed to decode\n", __func__);
+            for (auto * j : dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
+            continue;
+        }
+        for (auto * j : dev_jobs) j->after_device();
+    }
+    int ret = 0;
+    for (auto & j : jobs)
+        if (j.ret != 0 && ret == 0) ret = j.ret;
+    return ret;
+}
+
+}  // namespace wb

@@ -1,0 +1,245 @@
+"""Synthetic inputs for the transcription path: random-init Whisper models in the
+reference's on-disk ggml layout, and deterministic 16 kHz mono audio.
+
+There is no network, so no trained checkpoint exists here; BASELINE.json asks for
+"random-init weights of the named architecture".  The file layout written here is the one
+the reference loader parses (reader: sys/whisper.cpp/src/whisper.cpp:1513-1965, writer it
+mirrors: sys/whisper.cpp/models/convert-pt-to-ggml.py:268-339):
+
+    u32 magic 0x67676d6c | 11 x i32 hparams | i32 n_mel, i32 n_fft, f32 filters[n_mel*n_fft]
+    | i32 n_tokens, { u32 len, bytes } * n_tokens
+    | { i32 n_dims, i32 name_len, i32 ttype, i32 ne[n_dims] (reversed numpy shape), name, data } *
+
+The initialisation recipe (seeds and standard deviations) is a frozen test-design
+parameter: golden fixtures under tests/golden/ depend on it.
+"""
+from __future__ import annotations
+
+import io
+import struct
+from dataclasses import dataclass
+
+import numpy as np
+
+GGML_MAGIC = 0x67676D6C
+N_FFT_BINS = 201          # 1 + WHISPER_N_FFT/2   (whisper.h:33, whisper.cpp:3130)
+SAMPLE_RATE = 16000
+N_BASE_TOKENS = 50257     # tokens stored in the file; the loader synthesises the specials (whisper.cpp:1659-1690)
+
+
+@dataclass(frozen=True)
+class Arch:
+    name: str
+    n_vocab: int
+    n_audio_ctx: int
+    n_audio_state: int
+    n_audio_head: int
+    n_audio_layer: int
+    n_text_ctx: int
+    n_text_state: int
+    n_text_head: int
+    n_text_layer: int
+    n_mels: int
+
+    @property
+    def hparams(self):
+        return (self.n_vocab, self.n_audio_ctx, self.n_audio_state, self.n_audio_head, self.n_audio_layer,
+                self.n_text_ctx, self.n_text_state, self.n_text_head, self.n_text_layer, self.n_mels)
+
+
+def _arch(name, S, H, L, M=80, V=51865):
+    return Arch(name, V, 1500, S, H, L, 448, S, H, L, M)
+
+
+# SURVEY.md Appendix D (OpenAI Whisper dims; the reference infers the type from n_audio_layer, whisper.cpp:1543-1565)
+ARCHS = {
+    "tiny":     _arch("tiny", 384, 6, 4),
+    "base":     _arch("base", 512, 8, 6),
+    "small":    _arch("small", 768, 12, 12),
+    "medium":   _arch("medium", 1024, 16, 24),
+    "large-v3": _arch("large-v3", 1280, 20, 32, M=128, V=51866),
+    # reduced shapes for fast CPU-side tests (same layer structure, D=64 heads)
+    "micro":    Arch("micro", 51865, 1500, 128, 2, 2, 448, 128, 2, 2, 80),
+}
+
+
+def mel_filterbank(n_mels: int, n_fft: int = 400, sr: int = SAMPLE_RATE) -> np.ndarray:
+    """Deterministic Slaney-style triangular mel filterbank [n_mels, 201] (float32).
+
+    The real mel_filters.npz is not in the reference tree (convert-pt-to-ggml.py:221 reads
+    it from an OpenAI checkout), so the synthetic models carry this one.
+    """
+    n_bins = n_fft // 2 + 1
+    fft_freqs = np.linspace(0.0, sr / 2.0, n_bins)
+
+    def hz_to_mel(f):
+        f = np.asarray(f, dtype=np.float64)
+        mel = f / (200.0 / 3)
+        log_t = f >= 1000.0
+        mel = np.where(log_t, 15.0 + np.log(np.maximum(f, 1e-9) / 1000.0) / (np.log(6.4) / 27.0), mel)
+        return mel
+
+    def mel_to_hz(m):
+        m = np.asarray(m, dtype=np.float64)
+        f = m * (200.0 / 3)
+        log_t = m >= 15.0
+        f = np.where(log_t, 1000.0 * np.exp((np.log(6.4) / 27.0) * (m - 15.0)), f)
+        return f
+
+    mel_pts = mel_to_hz(np.linspace(hz_to_mel(0.0), hz_to_mel(sr / 2.0), n_mels + 2))
+    fdiff = np.diff(mel_pts)
+    ramps = mel_pts[:, None] - fft_freqs[None, :]
+    lower = -ramps[:-2] / fdiff[:-1, None]
+    upper = ramps[2:] / fdiff[1:, None]
+    w = np.maximum(0.0, np.minimum(lower, upper))
+    w *= (2.0 / (mel_pts[2:n_mels + 2] - mel_pts[:n_mels]))[:, None]
+    return w.astype(np.float32)
+
+
+def vocab_tokens():
+    """50,257 distinct byte strings; ids < 256 are the single bytes, so " " (id 32) exists
+    (the reference's suppress_blank does token_to_id.at(" "), whisper.cpp:6191)."""
+    toks = [bytes([i]) for i in range(256)]
+    toks[0] = b"<0>"  # avoid an embedded NUL: token text crosses the ABI as a C string
+    toks += [b" t%d" % i if i % 3 == 0 else b"t%d" % i for i in range(256, N_BASE_TOKENS)]
+    return toks
+
+
+def tensor_plan(a: Arch):
+    """(name, numpy shape, kind) in file order. kind: 'w' matrix (f16), 'b' bias, 'g' LN gamma,
+    'beta' LN beta, 'pe' positional embedding, 'te' token embedding, 'cw' conv weight, 'cb' conv bias.
+    Names: sys/whisper.cpp/src/whisper-arch.h:42-109."""
+    S, T, M, V = a.n_audio_state, a.n_audio_ctx, a.n_mels, a.n_vocab
+    plan = [
+        ("encoder.positional_embedding", (T, S), "pe"),
+        ("encoder.conv1.weight", (S, M, 3), "cw"), ("encoder.conv1.bias", (S, 1), "cb"),
+        ("encoder.conv2.weight", (S, S, 3), "cw"), ("encoder.conv2.bias", (S, 1), "cb"),
+        ("encoder.ln_post.weight", (S,), "g"), ("encoder.ln_post.bias", (S,), "beta"),
+    ]
+
+    def block(prefix, S, cross):
+        out = []
+        for ln in (["attn_ln", "cross_attn_ln", "mlp_ln"] if cross else ["attn_ln", "mlp_ln"]):
+            out += [(f"{prefix}.{ln}.weight", (S,), "g"), (f"{prefix}.{ln}.bias", (S,), "beta")]
+        for att in (["attn", "cross_attn"] if cross else ["attn"]):
+            out += [(f"{prefix}.{att}.query.weight", (S, S), "w"), (f"{prefix}.{att}.query.bias", (S,), "b"),
+                    (f"{prefix}.{att}.key.weight", (S, S), "w"),
+                    (f"{prefix}.{att}.value.weight", (S, S), "w"), (f"{prefix}.{att}.value.bias", (S,), "b"),
+                    (f"{prefix}.{att}.out.weight", (S, S), "w"), (f"{prefix}.{att}.out.bias", (S,), "b")]
+        out += [(f"{prefix}.mlp.0.weight", (4 * S, S), "w"), (f"{prefix}.mlp.0.bias", (4 * S,), "b"),
+                (f"{prefix}.mlp.2.weight", (S, 4 * S), "w"), (f"{prefix}.mlp.2.bias", (S,), "b")]
+        return out
+
+    for i in range(a.n_audio_layer):
+        plan += block(f"encoder.blocks.{i}", S, cross=False)
+    St = a.n_text_state
+    plan += [("decoder.positional_embedding", (a.n_text_ctx, St), "pe"),
+             ("decoder.token_embedding.weight", (V, St), "te"),
+             ("decoder.ln.weight", (St,), "g"), ("decoder.ln.bias", (St,), "beta")]
+    for i in range(a.n_text_layer):
+        plan += block(f"decoder.blocks.{i}", St, cross=True)
+    return plan
+
+
+@dataclass(frozen=True)
+class InitRecipe:
+    """Frozen initialisation recipe. `te_std` widens the argmax margins of the
+    tied-embedding logits; `gain` scales every projection matrix."""
+    seed: int = 1234
+    te_std: float = 0.05
+    gain: float = 1.0
+    bias_std: float = 0.02
+    pe_std: float = 0.02
+
+
+def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype: int = 1, with_tensors: bool = True) -> int:
+    """Write a random-init model to `out` (path or binary file object). Returns bytes written.
+
+    with_tensors=False writes the reference's own test convention: a header-only file with
+    zero tensor records, which its loader accepts (whisper.cpp:1959-1960)."""
+    a = ARCHS[arch] if isinstance(arch, str) else arch
+    own = isinstance(out, (str, bytes)) or hasattr(out, "__fspath__")
+    f = open(out, "wb") if own else out
+    n0 = f.tell()
+    try:
+        f.write(struct.pack("<I", GGML_MAGIC))
+        f.write(struct.pack("<11i", *a.hparams, ftype))
+        filt = mel_filterbank(a.n_mels)
+        f.write(struct.pack("<2i", a.n_mels, N_FFT_BINS))
+        f.write(filt.astype("<f4").tobytes())
+        toks = vocab_tokens()
+        f.write(struct.pack("<i", len(toks)))
+        for t in toks:
+            f.write(struct.pack("<I", len(t)))
+            f.write(t)
+        if with_tensors:
+            rng = np.random.default_rng(recipe.seed)
+            for name, shape, kind in tensor_plan(a):
+                n = int(np.prod(shape))
+                x = rng.standard_normal(n, dtype=np.float32).reshape(shape)
+                if kind == "w":
+                    x *= recipe.gain / np.sqrt(shape[1])
+                elif kind == "cw":
+                    x *= recipe.gain / np.sqrt(shape[1] * shape[2])
+                elif kind in ("b", "cb", "beta"):
+                    x *= recipe.bias_std
+                elif kind == "g":
+                    x = 1.0 + 0.02 * x
+                elif kind == "pe":
+                    x *= recipe.pe_std
+                elif kind == "te":
+                    x *= recipe.te_std
+                f16 = ftype == 1 and kind in ("w", "cw", "te")
+                data = x.astype("<f2" if f16 else "<f4")
+                nm = name.encode()
+                f.write(struct.pack("<3i", len(shape), len(nm), 1 if f16 else 0))
+                f.write(struct.pack(f"<{len(shape)}i", *reversed(shape)))
+                f.write(nm)
+                f.write(data.tobytes())
+        return f.tell() - n0
+    finally:
+        if own:
+            f.close()
+
+
+def model_bytes(arch, recipe: InitRecipe = InitRecipe(), **kw) -> bytes:
+    bio = io.BytesIO()
+    write_model(arch, bio, recipe, **kw)
+    return bio.getvalue()
+
+
+def synth_audio(seconds: float, seed: int = 12345, sr: int = SAMPLE_RATE) -> np.ndarray:
+    """Deterministic speech-band test signal in [-1, 1]: a few AM/FM-modulated tones with
+    syllable-rate envelopes plus low-level LCG white noise."""
+    n = int(round(seconds * sr))
+    t = np.arange(n, dtype=np.float64) / sr
+    rng = np.random.default_rng(seed)
+    x = np.zeros(n, dtype=np.float64)
+    for k in range(6):
+        f0 = rng.uniform(110.0, 2200.0)
+        fm = rng.uniform(0.2, 1.5)
+        am = rng.uniform(1.5, 6.0)
+        ph = rng.uniform(0, 2 * np.pi, 3)
+        env = 0.5 * (1.0 + np.sin(2 * np.pi * am * t + ph[0])) ** 2 / 2.0
+        x += (0.6 / (k + 1)) * env * np.sin(2 * np.pi * f0 * t + 4.0 * np.sin(2 * np.pi * fm * t + ph[1]) + ph[2])
+    # LCG noise (language-agnostic, reproducible without numpy's generator)
+    s = np.uint64(seed * 2654435761 % (1 << 32))
+    a, c = np.uint64(1664525), np.uint64(1013904223)
+    lcg = np.empty(n, dtype=np.float64)
+    state = int(s)
+    # vectorised LCG: x_k = a^k x_0 + c (a^k - 1)/(a - 1) mod 2^32, done in blocks to stay exact in Python ints
+    blk = 1 << 16
+    ak = [1]; ck = [0]
+    for _ in range(blk - 1):
+        ak.append((ak[-1] * 1664525) & 0xFFFFFFFF)
+        ck.append((ck[-1] * 1664525 + 1013904223) & 0xFFFFFFFF)
+    ak = np.array(ak, dtype=np.uint64); ck = np.array(ck, dtype=np.uint64)
+    for i0 in range(0, n, blk):
+        m = min(blk, n - i0)
+        vals = (ak[:m] * np.uint64(state) + ck[:m]) & np.uint64(0xFFFFFFFF)
+        lcg[i0:i0 + m] = vals.astype(np.float64) / 2147483648.0 - 1.0
+        state = int((int(ak[m - 1]) * state + int(ck[m - 1])) & 0xFFFFFFFF)
+        state = (state * 1664525 + 1013904223) & 0xFFFFFFFF
+    x += 0.02 * lcg
+    x *= 0.8 / max(1e-9, np.max(np.abs(x)))
+    return x.astype(np.float32)
