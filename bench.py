@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py — RTFx (audio-seconds per second) of the transcription hot path, large-v3 greedy, on N B200s.
+
+One "step" = one pass of the whole path (PCM -> log-mel -> encoder -> greedy decode loop -> segments) over one batch
+of `--batch` independent 30 s shards per GPU, through whisper_b200_full_batch (the lock-step form of
+whisper_full_with_state).  Weak scaling: every rank processes its own batch; there is no collective on the math path.
+
+  value : shards' PCM already resident in HBM when the timed region starts
+  e2e   : the same call with pinned HOST PCM (H2D inside the timed region) + reading every segment/token back
+  roofline : the dominant kernel category, timed in situ with CUDA events on the launching stream
+  cpu_baseline : the reference's own CPU engine (oracle/_ref) on a bounded sample, rank 0, N=1
+
+`--impl reference` times the reference CPU engine alone on the same config (one shard per step).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+from whisper_rust_b200 import (FullParams, SamplingStrategy, WhisperContext, WhisperContextParameters, api, synth)  # noqa: E402
+
+RECIPE = synth.InitRecipe(te_std=0.2)   # frozen test-design parameter (DESIGN.md "synthetic workload")
+CACHE = Path(os.environ.get("WB200_CACHE", "/tmp/wb200_cache"))
+
+
+def model_path(arch: str) -> Path:
+    CACHE.mkdir(parents=True, exist_ok=True)
+    p = CACHE / f"ggml-{arch}-seed{RECIPE.seed}-te{RECIPE.te_std}.bin"
+    if not p.exists():
+        tmp = p.with_suffix(f".tmp{os.getpid()}")
+        synth.write_model(arch, tmp, RECIPE)
+        os.replace(tmp, p)
+    return p
+
+
+def make_params(lib):
+    p = FullParams(lib, SamplingStrategy.GREEDY, best_of=1)
+    p.set_language("en").set_temperature_inc(0.0).set_n_threads(max(1, os.cpu_count() or 1))
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        busy = sorted(sm)[len(sm) // 2:]
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def read_results(states):
+    """device->host read of the step's result through the accessors; returns (token ids per state, bytes read)."""
+    out, nbytes = [], 0
+    for st in states:
+        ids = []
+        for i in range(st.full_n_segments()):
+            nbytes += 16 + len(st.full_get_segment_text(i) or b"")
+            for j in range(st.full_n_tokens(i)):
+                ids.append(st.full_get_token_id(i, j))
+                nbytes += 56
+        out.append(ids)
+    return out, nbytes
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's own CPU engine (oracle/_ref), one 30 s shard per step, all host threads."""
+    import conftest as cf
+    if rank != 0:
+        return
+    if not cf.ORACLE_LIB.exists():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libwhisper_ref.so was not built in this snapshot"}))
+        return
+    lib = api.load_library(cf.ORACLE_LIB)
+    api.install_quiet_logging(lib)
+    ctx = WhisperContext.new_with_params(model_path(args.model), WhisperContextParameters(use_gpu=False), lib=lib)
+    st = ctx.create_state()
+    p = make_params(lib)
+    cores = os.cpu_count() or 1
+    clips = [synth.synth_audio(args.seconds, seed=1000 + i) for i in range(args.warmup + args.steps)]
+    for i in range(args.warmup):
+        st.full(p, clips[i])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        st.full(p, clips[args.warmup + i])
+    dt = time.perf_counter() - t0
+    rtfx = args.steps * args.seconds / dt
+    print(json.dumps({
+        "impl": "reference", "metric": "RTFx (audio-s/s) greedy", "value": rtfx, "unit": "audio-s/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f16 operands / f32 accumulate", "data": "synthetic",
+        "config": {"workload": f"whisper {args.model} (random-init ggml layout) greedy best_of=1 temperature_inc=0, one 30 s synthetic "
+                               f"shard per step on the host CPU (reference ggml CPU path)", "model": args.model},
+        "cpu_baseline": {"value": rtfx, "unit": "audio-s/s", "cores": cores, "kind": "reference",
+                         "sample": f"{args.steps} x {args.seconds:.0f} s shards, n_threads={cores}"},
+        "e2e": {"value": rtfx, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="large-v3")
+    ap.add_argument("--batch", type=int, default=16, help="30 s shards per GPU per step")
+    ap.add_argument("--seconds", type=float, default=30.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import conftest as cf
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the b200 arm has no CPU path (use --impl reference for the CPU engine)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if rank == 0:
+        model_path(args.model)
+    barrier()
+    lib = cf.declare(api.load_library(), cf._B200_SIGS)
+    lib.whisper_b200_profile.argtypes = [C.c_int]
+    lib.whisper_b200_profile_read.restype = C.c_int
+    lib.whisper_b200_profile_read.argtypes = [C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64),
+                                              C.POINTER(C.c_uint64), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    api.install_quiet_logging(lib)
+    ctx = WhisperContext.new_with_params(model_path(args.model), WhisperContextParameters(use_gpu=True, gpu_device=local_rank), lib=lib)
+    B = args.batch
+    states = [ctx.create_state() for _ in range(B)]
+    st_arr = (C.c_void_p * B)(*[s.ptr for s in states])
+    p = make_params(lib)
+    n_samples = int(round(args.seconds * synth.SAMPLE_RATE))
+    ns_arr = (C.c_int * B)(*([n_samples] * B))
+
+    # distinct clips per rank and per step (a step never re-reads the previous step's audio)
+    n_sets = 2
+    host_sets, dev_sets = [], []
+    for k in range(n_sets):
+        clips = np.stack([synth.synth_audio(args.seconds, seed=1000 + rank * 100000 + k * B + i) for i in range(B)])
+        h = torch.from_numpy(clips).pin_memory()
+        host_sets.append(h)
+        dev_sets.append(h.cuda())
+
+    def ptrs(t):
+        return (C.POINTER(C.c_float) * B)(*[C.cast(t[i].data_ptr(), C.POINTER(C.c_float)) for i in range(B)])
+
+    def step(tensor_set):
+        r = lib.whisper_b200_full_batch(ctx.ptr, st_arr, B, p.fp, ptrs(tensor_set), ns_arr)
+        if r != 0:
+            raise SystemExit(f"whisper_b200_full_batch failed: {r}")
+
+    for i in range(args.warmup):
+        step(dev_sets[i % n_sets])
+
+    def timed(sets, read_back):
+        d2h = 0
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = lib.whisper_b200_kernel_launches()
+        e0.record()
+        for i in range(args.steps):
+            step(sets[i % n_sets])
+            if read_back:
+                _, nb = read_results(states)
+                d2h += nb
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = lib.whisper_b200_kernel_launches() - l0
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches, d2h // max(1, args.steps)
+
+    lib.whisper_b200_profile(20000)
+    with ClockSampler(local_rank) as clk:
+        ms_dev, launches, _ = timed(dev_sets, False)
+    cats = {}
+    ncat = lib.whisper_b200_profile_read(0, None, 0, None, None, None, None, None)
+    for c in range(ncat):
+        name = C.create_string_buffer(64)
+        ms, ns, nt, by, fl = C.c_double(), C.c_uint64(), C.c_uint64(), C.c_double(), C.c_double()
+        lib.whisper_b200_profile_read(c, name, 64, C.byref(ms), C.byref(ns), C.byref(nt), C.byref(by), C.byref(fl))
+        if nt.value:
+            cats[name.value.decode()] = {"ms_sampled": ms.value, "n_sampled": ns.value, "n_total": nt.value, "bytes": by.value, "flops": fl.value}
+    lib.whisper_b200_profile(0)
+    ms_e2e, _, d2h = timed(host_sets, True)
+
+    audio_s_per_step = B * args.seconds * world
+    value = audio_s_per_step * args.steps / (ms_dev / 1e3)
+    e2e = audio_s_per_step * args.steps / (ms_e2e / 1e3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
+        # estimated share of the step per category: mean sampled duration x total launches
+        est = {k: (v["ms_sampled"] / max(1, v["n_sampled"])) * v["n_total"] for k, v in cats.items()}
+        dom = max(est, key=est.get) if est else None
+        roofline = None
+        if dom:
+            v = cats[dom]
+            avg_ms = v["ms_sampled"] / max(1, v["n_sampled"])
+            tensor_bound = dom in ("gemm_encoder",)
+            if tensor_bound:
+                ach = v["flops"] / (v["ms_sampled"] / 1e3) / 1e12
+                roofline = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak}
+            else:
+                ach = v["bytes"] / (v["ms_sampled"] / 1e3) / 1e9
+                roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
+            roofline.update({"traffic": None, "avg_launch_ms": avg_ms, "launches_sampled": v["n_sampled"], "peak_source": peak_src,
+                             "share_of_step_est": est[dom] / max(1e-9, sum(est.values())),
+                             "algorithmic_bytes_per_launch": v["bytes"] / max(1, v["n_sampled"])})
+        out = {
+            "metric": "RTFx (audio-s/s) greedy", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 operands / f32 accumulate", "data": "synthetic",
+            "config": {"workload": f"whisper {args.model} (random-init ggml layout, seed {RECIPE.seed}, te_std {RECIPE.te_std}) greedy "
+                                   f"best_of=1 temperature_inc=0, {B} x {args.seconds:.0f} s synthetic shards per GPU per step via "
+                                   f"whisper_b200_full_batch; working set (weights + KV) >> L2, no flush needed",
+                       "model": args.model, "batch_per_gpu": B, "parallelism": f"shard-by-window x{world}"},
+            "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": B * n_samples * 4, "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clk.summary(),
+            "roofline": roofline,
+            "kernel_breakdown_ms_per_step_est": {k: round(x / args.steps, 3) for k, x in sorted(est.items(), key=lambda kv: -kv[1])},
+        }
+        if world == 1 and not args.no_cpu_baseline and cf.ORACLE_LIB.exists():
+            out["cpu_baseline"], out["parity"] = cpu_baseline(args, cf, states[0], host_sets[(args.steps - 1) % n_sets][0].numpy())
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, cf, gpu_state, clip):
+    """The reference CPU engine on ONE shard of the same workload (bounded sample), all host threads; also diffs its token
+    ids against what the CUDA path produced for the same shard in the last timed step."""
+    ref = api.load_library(cf.ORACLE_LIB)
+    api.install_quiet_logging(ref)
+    ctx = WhisperContext.new_with_params(model_path(args.model), WhisperContextParameters(use_gpu=False), lib=ref)
+    st = ctx.create_state()
+    p = make_params(ref)
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    st.full(p, clip)
+    dt = time.perf_counter() - t0
+    ids_ref, _ = read_results([st])
+    ids_gpu, _ = read_results([gpu_state])
+    same = ids_ref[0] == ids_gpu[0]
+    n_same = sum(1 for a, b in zip(ids_ref[0], ids_gpu[0]) if a == b)
+    base = {"value": args.seconds / dt, "unit": "audio-s/s", "cores": cores, "kind": "reference",
+            "sample": f"1 x {args.seconds:.0f} s shard of the same workload, n_threads={cores}, {dt:.1f} s wall"}
+    par = {"token_ids_identical": bool(same), "n_tokens_ref": len(ids_ref[0]), "n_tokens_b200": len(ids_gpu[0]), "n_equal_prefixwise": n_same}
+    st.free(); ctx.free()
+    return base, par
+
+
+if __name__ == "__main__":
+    main()

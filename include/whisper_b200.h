@@ -36,6 +36,13 @@ WHISPER_API int64_t whisper_b200_get_kv_cross(struct whisper_state * state, uint
 WHISPER_API int64_t whisper_b200_get_aheads_qk(struct whisper_state * state, float * dst, int64_t cap);              /* [n_heads][n_tok][T] */
 WHISPER_API void whisper_b200_get_counters(struct whisper_state * state, int32_t * counts7, int64_t * us6);          /* wc:868-881 */
 
+/* In-situ kernel timing: CUDA events on the launching stream around the first `max_samples_per_category` launches of each
+ * kernel category (0 switches it off).  whisper_b200_profile_read(0, ...) snapshots every category (device sync) and
+ * returns the category count; then read categories 1..count-1. */
+WHISPER_API void whisper_b200_profile(int max_samples_per_category);
+WHISPER_API int whisper_b200_profile_read(int category, char * name, int name_cap, double * ms_sum, uint64_t * n_sampled, uint64_t * n_total,
+                                          double * bytes_sampled /* algorithmic bytes of the sampled launches */, double * flops_sampled);
+
 /* number of kernels this library has launched in this process (all contexts) */
 WHISPER_API uint64_t whisper_b200_kernel_launches(void);
 WHISPER_API void whisper_b200_device_sync(struct whisper_context * ctx);

@@ -10,6 +10,7 @@
 #include "../../include/whisper_b200.h"
 #include "engine.h"
 #include "log.h"
+#include "prof.h"
 
 using namespace wb;
 
@@ -738,6 +739,24 @@ void whisper_b200_get_counters(struct whisper_state * s, int32_t * c, int64_t * 
     if (us) {
         us[0] = s->t_sample_us; us[1] = s->t_encode_us; us[2] = s->t_decode_us; us[3] = s->t_batchd_us; us[4] = s->t_prompt_us; us[5] = s->t_mel_us;
     }
+}
+void whisper_b200_profile(int max_samples_per_category) {
+    prof_enable(max_samples_per_category);
+    prof_reset();
+}
+int whisper_b200_profile_read(int category, char * name, int name_cap, double * ms_sum, uint64_t * n_sampled, uint64_t * n_total,
+                              double * bytes_sampled, double * flops_sampled) {
+    if (category < 0 || category >= PC_COUNT) return -1;
+    static double ms[PC_COUNT], by[PC_COUNT], fl[PC_COUNT];
+    static uint64_t ns[PC_COUNT], nt[PC_COUNT];
+    if (category == 0) prof_collect(ms, ns, nt, by, fl);  // reading category 0 snapshots all of them
+    if (name && name_cap > 0) snprintf(name, (size_t) name_cap, "%s", prof_cat_name(category));
+    if (ms_sum) *ms_sum = ms[category];
+    if (n_sampled) *n_sampled = ns[category];
+    if (n_total) *n_total = nt[category];
+    if (bytes_sampled) *bytes_sampled = by[category];
+    if (flops_sampled) *flops_sampled = fl[category];
+    return PC_COUNT;
 }
 uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count(); }
 void whisper_b200_device_sync(struct whisper_context * ctx) {

@@ -8,6 +8,7 @@
 #include <chrono>
 
 #include "log.h"
+#include "prof.h"
 
 namespace wb {
 
@@ -374,7 +375,7 @@ bool stage_pcm_to_mel(State & st, const float * samples, int n_samples) {
         WB_CUDA_OK(cudaMalloc((void **) &st.d_mel, need * sizeof(float)));
         st.mel_cap = need;
     }
-    WB_CUDA_OK(cudaMemcpyAsync(st.d_pcm, samples, (size_t) n_samples * sizeof(float), cudaMemcpyHostToDevice, ctx.stream));
+    WB_CUDA_OK(cudaMemcpyAsync(st.d_pcm, samples, (size_t) n_samples * sizeof(float), cudaMemcpyDefault /* host or device PCM */, ctx.stream));
     MelTables tab{ctx.model.mel_sin, ctx.model.mel_cos, ctx.model.mel_hann, ctx.model.mel_filters_t, n_mel};
     if (!mel_compute(tab, st.d_pcm, n_samples, n_len, st.d_mel, st.d_melmax, ctx.stream)) return false;
     WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
@@ -432,6 +433,7 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
     if (!ensure_enc_ws(ctx, W, T)) return false;
     EncWorkspace & ws = ctx.enc_ws;
     const int Tpad = ws.Tpad, R = W * T, F = 2 * T;  // F mel frames per window
+    g_prof_gemm_cat = PC_GEMM_ENC;
     cudaStream_t s = ctx.stream;
 
     for (int w = 0; w < W; ++w) {
@@ -667,6 +669,7 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
     const int T = rows[0].st->cross_T;
     for (int i = 1; i < n; ++i) WB_CHECK(rows[i].st->cross_T == T, "mixed audio contexts in one decode batch\n");
 
+    g_prof_gemm_cat = PC_GEMM_DEC;
     if (!embed_tokens(m.d_te, m.d_pe, d_tok, d_pos, n, S, ws.x, s)) return false;
     const float kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
     for (int il = 0; il < L; ++il) {
@@ -721,6 +724,7 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
             }
             a_rows = ws.att;
         }
+        g_prof_gemm_cat = PC_GEMM_LOGITS;
         GemmEpilogue e = epi_row(ws.logits, false, V);
         if (!gemm_f16_tc(opnd(a_rows, n_flag, S), opnd(m.d_te, V, S), n_flag, V, S, 1, e, 0, s)) return false;
     }

@@ -12,6 +12,7 @@
 // (sys/whisper.cpp/src/whisper.cpp:2131-2148,2212-2254,2321-2356,2558-2606,2657-2835) with the
 // rounding points of its CPU path: f16 operands, f32 accumulate (ggml-cpu.c:1269-1461).
 #include "gemm_tc.cuh"
+#include "prof.h"
 
 #include <atomic>
 #include <map>
@@ -305,6 +306,10 @@ static bool launch_gemm(const CUtensorMap & ta, const CUtensorMap & tb, int M, i
         attr_set = true;
     }
     dim3 grid(ceil_div(N, BN), ceil_div(M, BLOCK_M), batch);
+    ProfScope prof_scope(g_prof_gemm_cat, stream,
+                         (double) batch * ((double) M * K * taps.taps * 2 + (double) N * K * taps.taps * 2 * (b_bcast ? 1.0 / batch : 1.0) +
+                                          (double) M * N * (epi.out_f16 ? 2 : 4)),
+                         2.0 * batch * M * N * (double) K * taps.taps);
     gemm_f16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, smem, stream>>>(ta, tb, M, N, K, a_bcast, b_bcast, taps, epi);
     WB_CUDA_OK(cudaGetLastError());
     g_gemm_launches.fetch_add(1);

@@ -4,6 +4,7 @@
 // warp-shuffle reductions, not tensor cores.  Rounding points follow the reference's ggml CPU path
 //  so that greedy token ids match it.
 #include "kernels.cuh"
+#include "prof.h"
 
 #include <atomic>
 #include <math.h>
@@ -169,6 +170,7 @@ __global__ void mel_normalize_kernel(float * __restrict__ mel, int n_mel, int n_
 
 bool mel_compute(const MelTables & tab, const float * samples, int n_samples, int n_len, float * mel_out, int * scratch_max,
                  cudaStream_t stream) {
+    ProfScope prof_scope(PC_MEL, stream, (double) n_samples * 4 + (double) tab.n_mel * n_len * 4);
     WB_CHECK(tab.n_mel <= 128, "n_mel > 128 unsupported\n");
     const int n_eff   = n_samples + 200;
     const int n_valid = min(n_eff / HOP + 1, n_len);  // whisper.cpp:3133
@@ -215,6 +217,7 @@ __global__ void mel_window_kernel(const float * __restrict__ mel, int n_mel, int
 }
 
 bool mel_window_to_f16(const float * mel, int n_mel, int n_len, int offset, int n_frames, __half * out, int kc, cudaStream_t stream) {
+    ProfScope prof_scope(PC_MEL, stream);
     dim3 grid(ceil_div(n_frames, 32), ceil_div(kc, 32));
     mel_window_kernel<<<grid, dim3(32, 8), 0, stream>>>(mel, n_mel, n_len, offset, n_frames, out, kc);
     WB_LAUNCHED();
@@ -271,6 +274,7 @@ layernorm_kernel(const float * __restrict__ x, int rows, int S, const float * __
 
 bool layernorm_rows(const float * x, int rows, int S, const float * gamma, const float * beta, float eps, __half * out_f16,
                     float * out_f32, cudaStream_t stream) {
+    ProfScope prof_scope(PC_LN, stream, (double) rows * S * (4 + (out_f16 ? 2 : 0) + (out_f32 ? 4 : 0)));
     WB_CHECK((S & 3) == 0, "S must be a multiple of 4\n");
     if (rows <= 0) return true;
     layernorm_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(x, rows, S, gamma, beta, eps, out_f16, out_f32);
@@ -301,6 +305,7 @@ softmax_rows_kernel(const float * __restrict__ s, int64_t rows, int n, int64_t l
 }
 
 bool softmax_rows_f16(const float * s, int64_t rows, int n, int64_t lds, float scale, __half * p, int64_t ldp, cudaStream_t stream) {
+    ProfScope prof_scope(PC_ENC_SOFTMAX, stream, (double) rows * n * 6);
     if (rows <= 0) return true;
     softmax_rows_kernel<<<(unsigned) ceil_div64(rows, 8), 256, 0, stream>>>(s, rows, n, lds, scale, p, ldp);
     WB_LAUNCHED();
@@ -320,6 +325,7 @@ __global__ void embed_kernel(const __half * __restrict__ te, const float * __res
 
 bool embed_tokens(const __half * te, const float * pe, const int * tokens, const int * pos, int n_tokens, int S, float * x,
                   cudaStream_t stream) {
+    ProfScope prof_scope(PC_EMBED, stream);
     embed_kernel<<<n_tokens, 256, 0, stream>>>(te, pe, tokens, pos, S, x);
     WB_LAUNCHED();
     return true;
@@ -342,6 +348,7 @@ __global__ void self_kv_store_kernel(const __half * __restrict__ qkv, const Self
 }
 
 bool self_kv_store(const __half * qkv, const SelfKvRow * rows, int n_tokens, int S, int layer, cudaStream_t stream) {
+    ProfScope prof_scope(PC_SELF_ATTN, stream);
     self_kv_store_kernel<<<n_tokens, 128, 0, stream>>>(qkv, rows, S, layer);
     WB_LAUNCHED();
     return true;
@@ -416,6 +423,7 @@ self_attn_kernel(const __half * __restrict__ qkv, const SelfKvRow * __restrict__
 
 bool self_attn_decode(const __half * qkv, const SelfKvRow * rows, int n_tokens, int S, int H, int layer, __half * out,
                       cudaStream_t stream) {
+    ProfScope prof_scope(PC_SELF_ATTN, stream);
     // scores buffer sized for the largest cache the reference can build: 8+2 decoders x 512 cells (whisper.cpp:7101-7106)
     const int smem = 5120 * (int) sizeof(float);
     self_attn_kernel<<<dim3(H, n_tokens), 128, smem, stream>>>(qkv, rows, S, layer, out);
@@ -541,6 +549,7 @@ cross_attn_kernel(const __half * __restrict__ q, int ldq, const CrossKvRow * __r
 
 bool cross_attn_decode(const __half * q, int ldq, const CrossKvRow * rows, int n_tokens, int H, int T, int layer, float scale,
                        const int * ahead_slot, __half * out, int ldo, cudaStream_t stream) {
+    ProfScope prof_scope(PC_CROSS_ATTN, stream, (double) n_tokens * H * T * 64 * 2 * 2 /*K and V panels, f16*/, (double) n_tokens * H * T * 64 * 4);
     cross_attn_kernel<<<dim3(H, n_tokens), XA_THREADS, T * (int) sizeof(float), stream>>>(q, ldq, rows, H, T, layer, scale, ahead_slot,
                                                                                          out, ldo);
     WB_LAUNCHED();
@@ -733,6 +742,7 @@ sampler_kernel(SamplerStatic st, const float * __restrict__ logits_all, int64_t 
 
 bool sample_rows(const SamplerStatic & st, const float * logits, int64_t ld_logits, const SamplerRow * rows, int n_rows, float * work,
                  SamplerOut * out, cudaStream_t stream) {
+    ProfScope prof_scope(PC_SAMPLER, stream);
     if (n_rows <= 0) return true;
     sampler_kernel<<<n_rows, SM_THREADS, 0, stream>>>(st, logits, ld_logits, rows, work, out);
     WB_LAUNCHED();
@@ -875,6 +885,7 @@ dtw_wavefront_kernel(const float * __restrict__ x, int N, int M, float * __restr
 
 bool dtw_cost(const float * qk, int n_heads, int n_tok, int T, int n_audio, int medfilt_width, float * work_nrm, float * work_cost,
               cudaStream_t stream) {
+    ProfScope prof_scope(PC_DTW, stream);
     WB_CHECK(medfilt_width <= 15 && (medfilt_width & 1), "bad median filter width %d\n", medfilt_width);
     dtw_norm_kernel<<<dim3(ceil_div(n_audio, 128), n_heads), 128, 0, stream>>>(qk, n_tok, T, n_audio, work_nrm);
     WB_LAUNCHED();
@@ -885,6 +896,7 @@ bool dtw_cost(const float * qk, int n_heads, int n_tok, int T, int n_audio, int 
 }
 
 bool dtw_path(const float * cost, int N, int M, float * diag3, int8_t * trace, int * path, int * path_len, cudaStream_t stream) {
+    ProfScope prof_scope(PC_DTW, stream);
     dtw_wavefront_kernel<<<1, 256, 0, stream>>>(cost, N, M, diag3, trace, path, path_len);
     WB_LAUNCHED();
     return true;

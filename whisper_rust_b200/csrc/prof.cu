@@ -1,0 +1,88 @@
+#include "prof.h"
+
+#include <mutex>
+#include <vector>
+
+namespace wb {
+
+static const char * k_names[PC_COUNT] = {"mel", "gemm_encoder", "encoder_softmax", "layernorm", "gemm_decoder", "gemm_logits",
+                                         "self_attn_decode", "cross_attn_decode", "sampler", "embed", "dtw", "other"};
+const char * prof_cat_name(int cat) { return cat >= 0 && cat < PC_COUNT ? k_names[cat] : "?"; }
+
+int g_prof_gemm_cat = PC_OTHER;
+
+namespace {
+struct Cat {
+    std::vector<cudaEvent_t> ev;  // pairs
+    uint64_t total = 0;
+    double bytes = 0.0, flops = 0.0;
+    int used = 0;  // pairs in use
+};
+std::mutex g_mu;
+int g_max = 0;
+Cat g_cat[PC_COUNT];
+}  // namespace
+
+void prof_enable(int max_samples_per_cat) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_max = max_samples_per_cat;
+}
+
+void prof_reset() {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (auto & c : g_cat) {
+        c.total = 0;
+        c.used = 0;
+        c.bytes = c.flops = 0.0;
+    }
+}
+
+ProfScope::ProfScope(int cat_, cudaStream_t s_, double bytes, double flops) : cat(cat_), s(s_), slot(-1) {
+    if (g_max <= 0) return;
+    std::lock_guard<std::mutex> lk(g_mu);
+    Cat & c = g_cat[cat];
+    c.total++;
+    // sample every launch until the cap, then every 16th launch into a rotating window is not needed: a prefix of
+    // g_max launches of each category is representative for steady-state loops
+    if (c.used >= g_max) return;
+    if ((int) c.ev.size() < 2 * (c.used + 1)) {
+        cudaEvent_t a, b;
+        if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+        c.ev.push_back(a);
+        c.ev.push_back(b);
+    }
+    slot = c.used++;
+    c.bytes += bytes;
+    c.flops += flops;
+    cudaEventRecord(c.ev[2 * slot], s);
+}
+
+ProfScope::~ProfScope() {
+    if (slot < 0) return;
+    std::lock_guard<std::mutex> lk(g_mu);
+    cudaEventRecord(g_cat[cat].ev[2 * slot + 1], s);
+}
+
+void prof_collect(double * ms_sum, uint64_t * n_sampled, uint64_t * n_total, double * bytes_sampled, double * flops_sampled) {
+    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int k = 0; k < PC_COUNT; ++k) {
+        Cat & c = g_cat[k];
+        double sum = 0.0;
+        int n = 0;
+        for (int i = 0; i < c.used; ++i) {
+            float ms = 0.0f;
+            if (cudaEventElapsedTime(&ms, c.ev[2 * i], c.ev[2 * i + 1]) == cudaSuccess) {
+                sum += ms;
+                ++n;
+            }
+        }
+        ms_sum[k] = sum;
+        n_sampled[k] = (uint64_t) n;
+        n_total[k] = c.total;
+        bytes_sampled[k] = c.bytes;
+        flops_sampled[k] = c.flops;
+    }
+}
+
+}  // namespace wb
