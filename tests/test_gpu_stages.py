@@ -83,8 +83,11 @@ def test_encoder_matches_oracle(prod_lib, ref_lib, arch):
     assert np.argmax(res["b200_logits"]) == np.argmax(res["ref_logits"])
 
 
-def _run_full(lib, gpu, arch, pcm, strategy=SamplingStrategy.GREEDY, tinc=0.0, **kw):
-    ctx = _ctx(lib, arch, gpu)
+RICH = synth.InitRecipe(te_std=0.2, pe_std=0.3, gain=3.0, ts_scale=1.6)
+
+
+def _run_full(lib, gpu, arch, pcm, strategy=SamplingStrategy.GREEDY, tinc=0.0, recipe=RECIPE, dtw=None, **kw):
+    ctx = WhisperContext.new_from_buffer_with_params(model_blob(arch, recipe), WhisperContextParameters(use_gpu=gpu, dtw_parameters=dtw), lib=lib)
     st = ctx.create_state()
     p = FullParams(lib, strategy, **kw)
     p.set_n_threads(8).set_language("en").set_temperature_inc(tinc)
@@ -94,15 +97,23 @@ def _run_full(lib, gpu, arch, pcm, strategy=SamplingStrategy.GREEDY, tinc=0.0, *
     return segs
 
 
-@pytest.mark.parametrize("arch,seconds", [("micro", 11.0), ("tiny", 30.0)])
-def test_full_greedy_tokens_match_oracle(prod_lib, ref_lib, arch, seconds):
-    pcm = synth.synth_audio(seconds, seed=3)
-    a = _run_full(ref_lib, False, arch, pcm, best_of=1)
-    b = _run_full(prod_lib, True, arch, pcm, best_of=1)
-    print(len(a), len(b), [t["id"] for s in a for t in s.tokens][:20], [t["id"] for s in b for t in s.tokens][:20])
+def _same(a, b, p_rtol=2e-2):
     assert len(a) == len(b)
     for sa, sb in zip(a, b):
         assert (sa.t0, sa.t1, sa.text) == (sb.t0, sb.t1, sb.text)
         assert [t["id"] for t in sa.tokens] == [t["id"] for t in sb.tokens]
         assert [t["tid"] for t in sa.tokens] == [t["tid"] for t in sb.tokens]
-        np.testing.assert_allclose([t["p"] for t in sa.tokens], [t["p"] for t in sb.tokens], rtol=2e-2, atol=1e-4)
+        assert [t["t_dtw"] for t in sa.tokens] == [t["t_dtw"] for t in sb.tokens]
+        np.testing.assert_allclose([t["p"] for t in sa.tokens], [t["p"] for t in sb.tokens], rtol=p_rtol, atol=1e-4)
+
+
+# Cases are chosen so that the oracle's smallest top-1/top-2 logit gap over the whole decode (recorded in
+# tests/golden/full_transcripts.json) is >= 2e-3: below ~1e-4 the winner depends on fp32 summation order, which differs even
+# between two ISA builds of the reference itself (DESIGN.md "parity").
+@pytest.mark.parametrize("arch,recipe,seconds,seed", [("tiny", RECIPE, 30.0, 3), ("mini", RICH, 47.3, 5), ("mini", RICH, 30.0, 4),
+                                                      ("mini", RICH, 11.0, 3), ("mini", RICH, 0.3, 6)])
+def test_full_greedy_tokens_match_oracle(prod_lib, ref_lib, arch, recipe, seconds, seed):
+    pcm = synth.synth_audio(seconds, seed=seed)
+    a = _run_full(ref_lib, False, arch, pcm, recipe=recipe, best_of=1)
+    b = _run_full(prod_lib, True, arch, pcm, recipe=recipe, best_of=1)
+    _same(a, b)

@@ -59,7 +59,10 @@ ARCHS = {
     "medium":   _arch("medium", 1024, 16, 24),
     "large-v3": _arch("large-v3", 1280, 20, 32, M=128, V=51866),
     # reduced shapes for fast CPU-side tests (same layer structure, D=64 heads)
+    # (micro has 2 text layers, so the reference treats it as a first-release distilled model and forces no_timestamps,
+    #  whisper.cpp:6956-6960; mini has 3 and keeps the timestamp logic live)
     "micro":    Arch("micro", 51865, 1500, 128, 2, 2, 448, 128, 2, 2, 80),
+    "mini":     Arch("mini", 51865, 1500, 192, 3, 2, 448, 192, 3, 3, 80),
 }
 
 
@@ -150,6 +153,8 @@ class InitRecipe:
     gain: float = 1.0
     bias_std: float = 0.02
     pe_std: float = 0.02
+    ts_scale: float = 1.0   # multiplies the token-embedding rows of the timestamp tokens (ids >= 50364): > 1 makes the
+                            # sampler emit timestamps, hence several segments / windows per clip (test-design parameter)
 
 
 def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype: int = 1, with_tensors: bool = True) -> int:
@@ -189,6 +194,8 @@ def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype:
                     x *= recipe.pe_std
                 elif kind == "te":
                     x *= recipe.te_std
+                    if recipe.ts_scale != 1.0:
+                        x[N_BASE_TOKENS + 107:] *= recipe.ts_scale
                 f16 = ftype == 1 and kind in ("w", "cw", "te")
                 data = x.astype("<f2" if f16 else "<f4")
                 nm = name.encode()
