@@ -56,6 +56,18 @@ WHISPER_API int whisper_b200_test_mel(struct whisper_context * ctx, const float 
 /* the decode-step cross-attention kernel on device buffers: q f16 [n][S], kv f16 [2H][T][64] per row (same kv for all rows) */
 WHISPER_API int whisper_b200_test_cross_attn(const void * q_f16, const void * kv_f16, void * out_f16, int n_rows, int n_head, int n_ctx);
 
+/* decode-step kernels (step.cu): weight-streaming tcgen05 GEMM out[n][n_out] = x[n][k] . w[n_out][k]^T (+bias), n <= 256;
+ * force_split: 0 auto split-K, 1 direct epilogue, >1 that many k-splits */
+WHISPER_API int whisper_b200_test_gemm_wstream(const void * w_f16, const void * x_f16, float * out, int n, int n_out, int k, const float * bias,
+                                               int force_split);
+/* the TMA-streamed decode-step cross attention: same contract as whisper_b200_test_cross_attn */
+WHISPER_API int whisper_b200_test_cross_attn_step(const void * q_f16, const void * kv_f16, void * out_f16, int n_rows, int n_head, int n_ctx);
+/* micro-benchmarks, CUDA-event timed on the launching stream, graph-replayed so that launch overhead is excluded:
+ *   "cross_attn_step": a = heads, b = audio ctx, c = layers (n_rows sequences, each with its own cross cache)
+ *   "gemm_wstream"   : a = n_out, b = k, c = number of distinct weight matrices streamed round-robin */
+WHISPER_API int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c, int iters, double * us_per_launch,
+                                          double * bytes_per_launch);
+
 #ifdef __cplusplus
 }
 #endif

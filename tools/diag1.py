@@ -5,7 +5,7 @@ import numpy as np
 import conftest as cf
 from conftest import *
 from whisper_rust_b200 import *
-R = synth.InitRecipe(te_std=0.2)
+R = synth.InitRecipe(te_std=0.2) if (len(sys.argv) < 3 or sys.argv[2] != 'rich') else synth.InitRecipe(te_std=0.2, pe_std=0.3, gain=3.0, ts_scale=1.6)
 ref = api.load_library(ORACLE_LIB); declare(ref, cf._PROBE_SIGS); api.install_quiet_logging(ref)
 prod = api.load_library(); declare(prod, cf._B200_SIGS); api.install_quiet_logging(prod)
 arch = sys.argv[1] if len(sys.argv) > 1 else 'tiny'

@@ -9,6 +9,7 @@
 
 #include "../../include/whisper_b200.h"
 #include "engine.h"
+#include "step.cuh"
 #include "log.h"
 #include "prof.h"
 
@@ -758,7 +759,7 @@ int whisper_b200_profile_read(int category, char * name, int name_cap, double * 
     if (flops_sampled) *flops_sampled = fl[category];
     return PC_COUNT;
 }
-uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count(); }
+uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count() + step_launch_count(); }
 void whisper_b200_device_sync(struct whisper_context * ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->model.device);
@@ -795,12 +796,37 @@ int whisper_b200_test_cross_attn(const void * q, const void * kv, void * out, in
         cudaFree(d_rows);
         if (cudaMalloc((void **) &d_rows, (size_t) n_rows * sizeof(CrossKvRow)) != cudaSuccess) return 1;
         cap = n_rows;
+    }
+    {
         std::vector<CrossKvRow> h((size_t) n_rows);
         for (auto & r : h) r = CrossKvRow{(const __half *) kv, nullptr, 0, 0};
         if (cudaMemcpy(d_rows, h.data(), h.size() * sizeof(CrossKvRow), cudaMemcpyHostToDevice) != cudaSuccess) return 1;
     }
     const float scale = (float) pow(64.0, -0.25);
     return cross_attn_decode((const __half *) q, n_head * 64, d_rows, n_rows, n_head, n_ctx, 0, scale, nullptr, (__half *) out, n_head * 64, 0) ? 0 : 1;
+    WB_CATCH(3)
+}
+
+int whisper_b200_test_gemm_wstream(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int force_split) {
+    WB_TRY
+    return test_gemm_wstream((const __half *) w, (const __half *) x, out, n, n_out, k, bias, force_split) ? 0 : 1;
+    WB_CATCH(3)
+}
+int whisper_b200_test_cross_attn_step(const void * q, const void * kv, void * out, int n_rows, int n_head, int n_ctx) {
+    WB_TRY
+    return test_cross_attn_step((const __half *) q, (const __half *) kv, (__half *) out, n_rows, n_head, n_ctx) ? 0 : 1;
+    WB_CATCH(3)
+}
+int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c, int iters, double * us_per_launch, double * bytes_per_launch) {
+    WB_TRY
+    StepBenchResult r{};
+    bool ok = false;
+    if (strcmp(kind, "cross_attn_step") == 0) ok = bench_cross_attn_step(n_rows, a /*H*/, b /*T*/, c /*layers*/, iters, &r);
+    else if (strcmp(kind, "gemm_wstream") == 0) ok = bench_gemm_wstream(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
+    if (!ok) return 1;
+    if (us_per_launch) *us_per_launch = r.us_per_launch;
+    if (bytes_per_launch) *bytes_per_launch = r.bytes_per_launch;
+    return 0;
     WB_CATCH(3)
 }
 

@@ -9,6 +9,7 @@
 
 #include "log.h"
 #include "prof.h"
+#include "step.cuh"
 
 namespace wb {
 
@@ -109,6 +110,7 @@ State::~State() {
 Context::~Context() {
     cudaSetDevice(model.device);
     if (stream) cudaStreamSynchronize(stream);
+    step_release(*this);
     cudaFree(enc_ws.base);
     cudaFree(dec_ws.base);
     if (dec_ws.h_stage) cudaFreeHost(dec_ws.h_stage);

@@ -157,6 +157,7 @@ struct Context {
     std::mutex mu;  // serialises device work issued through this context's shared workspaces
     EncWorkspace enc_ws;
     DecWorkspace dec_ws;
+    void * step = nullptr;  // decode-step graphs + their workspace (step.cu)
 
     // alignment heads (wc:417-443, 8623-8642): per layer, slot index per head or -1
     int n_aheads = 0;

@@ -16,6 +16,7 @@
 
 #include "engine.h"
 #include "log.h"
+#include "step.cuh"
 
 namespace wb {
 
@@ -979,7 +980,14 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         if (!any_live) break;
         if (dev_jobs.empty()) continue;
 
-        bool ok = stage_decode(*ctx, rows.data(), (int) rows.size(), false);
+        bool ok;
+        const bool fused_step = step_eligible(*ctx, rows.data(), (int) rows.size(), any_dists) && rows.size() == srows.size();
+        if (fused_step) {
+            // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
+            ok = stage_step(*ctx, rows.data(), (int) rows.size(), sst, srows.data(), sdecs.data());
+        } else {
+            ok = stage_decode(*ctx, rows.data(), (int) rows.size(), false);
+        }
         if (ok && params_in.logits_filter_callback) {
             // the callback sees host logits between the static suppressions and the timestamp rules (wc:6226-6228):
             // not supported on the device sampler path
@@ -987,7 +995,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             if (!warned) log_msg(GGML_LOG_LEVEL_WARN, "%s: logits_filter_callback is ignored by the device sampler\n", __func__);
             warned = true;
         }
-        ok = ok && stage_sample(*ctx, sst, srows.data(), (int) srows.size(), any_dists, sdecs.data());
+        if (!fused_step) ok = ok && stage_sample(*ctx, sst, srows.data(), (int) srows.size(), any_dists, sdecs.data());
         if (!ok) {
             log_error("%s: failed to decode\n", __func__);
             for (auto * j : dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);

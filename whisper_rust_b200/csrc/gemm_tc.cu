@@ -293,7 +293,26 @@ static bool make_tmap(CUtensorMap * out, const GemmOperand & op, int K, int box_
     return true;
 }
 
+// plain 2-D K-major f16 matrix [rows][inner] (row stride in elements), 128-byte swizzle, box {box_inner (<= 64), box_rows (<= 256)}
+bool tmap_encode_2d(CUtensorMap * out, const void * ptr, uint64_t inner, uint64_t rows, uint64_t row_stride, uint32_t box_inner,
+                    uint32_t box_rows) {
+    PFN_encodeTiled enc = get_encode_fn();
+    WB_CHECK(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable\n");
+    WB_CHECK(((uintptr_t) ptr & 15) == 0 && (row_stride * 2) % 16 == 0, "tensor map operand must be 16-byte aligned\n");
+    WB_CHECK(box_inner * 2 <= 128 && box_rows <= 256 && box_rows >= 1, "bad TMA box %u x %u\n", box_inner, box_rows);
+    cuuint64_t dims[2]    = {(cuuint64_t) inner, (cuuint64_t) rows};
+    cuuint64_t strides[1] = {(cuuint64_t) row_stride * 2};
+    cuuint32_t box[2]     = {box_inner, box_rows};
+    cuuint32_t estr[2]    = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *) ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    WB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d) failed: %d (inner=%llu rows=%llu stride=%llu box=%ux%u)\n", (int) r,
+             (unsigned long long) inner, (unsigned long long) rows, (unsigned long long) row_stride, box_inner, box_rows);
+    return true;
+}
+
 static std::atomic<uint64_t> g_gemm_launches{0};
+void gemm_launch_count_add(uint64_t n) { g_gemm_launches.fetch_add(n); }
 uint64_t gemm_launch_count() { return g_gemm_launches.load(); }
 
 template <int BN>

@@ -66,5 +66,9 @@ bool gemm_f16_tc(const GemmOperand & A, const GemmOperand & B, int M, int N, int
                  int block_n, cudaStream_t stream, const GemmTaps * taps = nullptr);
 
 uint64_t gemm_launch_count();
+void gemm_launch_count_add(uint64_t n);  // launches issued through CUDA graphs
+
+bool tmap_encode_2d(CUtensorMap * out, const void * ptr, uint64_t inner, uint64_t rows, uint64_t row_stride, uint32_t box_inner,
+                    uint32_t box_rows);
 
 }  // namespace wb

@@ -20,12 +20,18 @@ struct Cat {
 };
 std::mutex g_mu;
 int g_max = 0;
+int g_suspended = 0;
 Cat g_cat[PC_COUNT];
 }  // namespace
 
 void prof_enable(int max_samples_per_cat) {
     std::lock_guard<std::mutex> lk(g_mu);
     g_max = max_samples_per_cat;
+}
+
+void prof_suspend(bool on) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_suspended += on ? 1 : -1;
 }
 
 void prof_reset() {
@@ -40,6 +46,7 @@ void prof_reset() {
 ProfScope::ProfScope(int cat_, cudaStream_t s_, double bytes, double flops) : cat(cat_), s(s_), slot(-1) {
     if (g_max <= 0) return;
     std::lock_guard<std::mutex> lk(g_mu);
+    if (g_suspended > 0) return;
     Cat & c = g_cat[cat];
     c.total++;
     // sample every launch until the cap, then every 16th launch into a rotating window is not needed: a prefix of

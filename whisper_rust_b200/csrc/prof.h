@@ -15,6 +15,7 @@ const char * prof_cat_name(int cat);
 
 void prof_enable(int max_samples_per_cat);  // 0 disables
 void prof_reset();
+void prof_suspend(bool on);  // no event records while a stream capture is in progress
 // returns sampled-milliseconds sum, sampled count and total launch count per category (arrays of PC_COUNT)
 void prof_collect(double * ms_sum, uint64_t * n_sampled, uint64_t * n_total, double * bytes_sampled, double * flops_sampled);
 

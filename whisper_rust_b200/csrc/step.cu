@@ -1,0 +1,1087 @@
+// The greedy decode step as one CUDA graph of weight-streaming kernels.  See step.cuh.
+#include "step.cuh"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <map>
+#include <vector>
+
+#include "log.h"
+#include "prof.h"
+
+namespace wb {
+
+// =============================================================================================
+// gemm_wstream:  Y[t][f] = sum_k X[t][k] * W[f][k]      (t < n <= 256 token rows, f < N_out weight rows)
+// =============================================================================================
+// The WEIGHT tile is the UMMA M operand (128 weight rows per CTA), the token rows are the N operand, so the
+// accumulator is D[128 features (TMEM lanes)][n_pad tokens (TMEM columns)].  grid = (ceil(N_out/128), split):
+// CTA (tile, s) reduces k-blocks [s*kb_per_split, ...) and either stores its f32 partial tile to
+// partial[s][t][f] (mode 0; the consumer kernel sums the splits in index order, deterministically) or, when
+// split == 1, applies bias / GELU and stores f16 or f32 directly (mode 1).
+// Rounding points as the reference's mul_mat (ggml-cpu.c:1269-1461): f16 operands, f32 accumulate.
+struct WsArgs {
+    int n, n_pad, N_out;
+    int kb_total, kb_per_split, stages;
+    int mode;  // 0: partial, 1: direct
+    float * partial;
+    int64_t split_stride;  // elements between splits = n * N_out
+    void * out;
+    int out_f16;
+    int64_t ldo;
+    const float * bias;
+    const __half * gelu_table;
+    uint32_t tmem_cols;
+};
+
+static constexpr int WS_THREADS = 192;
+static constexpr int WS_A_BYTES = 128 * 64 * 2;
+
+__device__ __forceinline__ float gelu_f16table(float x, const __half * __restrict__ table) {
+    // ggml_vec_gelu_f32 with GGML_GELU_FP16 (ggml-cpu/vec.h:571-585)
+    if (x <= -10.0f) return 0.0f;
+    if (x >= 10.0f) return x;
+    return __half2float(__ldg(table + __half_as_ushort(__float2half_rn(x))));
+}
+
+__global__ void __launch_bounds__(WS_THREADS, 2)
+gemm_wstream_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, WsArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    const int b_bytes     = a.n_pad * 128;
+    const int stage_bytes = WS_A_BYTES + b_bytes;
+    uint64_t * full_bar   = (uint64_t *) (smem + a.stages * stage_bytes);
+    uint64_t * empty_bar  = full_bar + a.stages;
+    uint64_t * tmem_full  = empty_bar + a.stages;
+    uint32_t * tmem_slot  = (uint32_t *) (tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f0    = blockIdx.x * 128;
+    const int split = blockIdx.y;
+    const int kb0   = split * a.kb_per_split;
+    const int nkb   = min(a.kb_per_split, a.kb_total - kb0);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_w);
+        tma_prefetch_desc(&tmap_x);
+        for (int s = 0; s < a.stages; ++s) {
+            mbar_init(full_bar + s, 1);
+            mbar_init(empty_bar + s, 1);
+        }
+        mbar_init(tmem_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc_rt(tmem_slot, a.tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    // PDL: every kernel of the step waits (griddepcontrol.wait) before it touches mutable global memory, so the next
+    // kernel may become resident now and overlap its prologue + weight prefetch with this kernel's tail
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint64_t pol_w = l2_policy_evict_first(), pol_x = l2_policy_evict_last();
+            // the weights do not depend on the previous kernel: start streaming them before the PDL wait
+            const int pre = min(nkb, a.stages);
+            for (int i = 0; i < pre; ++i) {
+                mbar_expect_tx(full_bar + i, stage_bytes);
+                tma_load_2d_hint(smem + i * stage_bytes, &tmap_w, full_bar + i, (kb0 + i) * 64, f0, pol_w);
+            }
+            pdl_wait();
+            for (int i = 0; i < pre; ++i)
+                tma_load_2d_hint(smem + i * stage_bytes + WS_A_BYTES, &tmap_x, full_bar + i, (kb0 + i) * 64, 0, pol_x);
+            int stage = pre == a.stages ? 0 : pre;
+            uint32_t phase = pre == a.stages ? 1 : 0;
+            for (int i = pre; i < nkb; ++i) {
+                mbar_wait(empty_bar + stage, phase ^ 1);
+                uint8_t * sa = smem + stage * stage_bytes;
+                mbar_expect_tx(full_bar + stage, stage_bytes);
+                tma_load_2d_hint(sa, &tmap_w, full_bar + stage, (kb0 + i) * 64, f0, pol_w);
+                tma_load_2d_hint(sa + WS_A_BYTES, &tmap_x, full_bar + stage, (kb0 + i) * 64, 0, pol_x);
+                if (++stage == a.stages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            const uint32_t idesc = umma_idesc_f16(128, (uint32_t) a.n_pad);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = 0; i < nkb; ++i) {
+                mbar_wait(full_bar + stage, phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+                const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + WS_A_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base, da + (uint64_t) (2 * k), db + (uint64_t) (2 * k), idesc, (i | k) != 0);
+                umma_commit(empty_bar + stage);
+                if (++stage == a.stages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            umma_commit(tmem_full);
+        }
+    } else {
+        // epilogue warps 2..5: TMEM lane group = warp % 4; lane = weight row (feature), column = token
+        const int grp = warp & 3;
+        const int f   = f0 + grp * 32 + lane;
+        pdl_wait();  // the output buffers may still be read by the previous kernel
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const bool f_ok = f < a.N_out;
+        float bias = 0.0f;
+        if (a.mode == 1 && a.bias != nullptr && f_ok) bias = __ldg(a.bias + f);
+        float * pout = a.partial + (int64_t) split * a.split_stride + f;
+#pragma unroll 1
+        for (int c0 = 0; c0 < a.n_pad; c0 += 16) {
+            if (c0 >= a.n) break;  // warp-uniform
+            uint32_t r[16];
+            tmem_ld_32x16(tmem_base + ((uint32_t) (grp * 32) << 16) + (uint32_t) c0, r);
+            tmem_ld_wait();
+            if (f_ok) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int t = c0 + j;
+                    if (t < a.n) {
+                        float v = __uint_as_float(r[j]);
+                        if (a.mode == 0) {
+                            pout[(int64_t) t * a.N_out] = v;
+                        } else {
+                            v = __fadd_rn(v, bias);
+                            if (a.gelu_table != nullptr) v = gelu_f16table(v, a.gelu_table);
+                            if (a.out_f16) ((__half *) a.out)[(int64_t) t * a.ldo + f] = __float2half_rn(v);
+                            else ((float *) a.out)[(int64_t) t * a.ldo + f] = v;
+                        }
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_rt(tmem_base, a.tmem_cols);
+    }
+}
+
+// ---- host side: plan (split / stages) and launch --------------------------------------------------------------
+static std::atomic<uint64_t> g_step_launches{0};
+static bool g_pdl = true;  // launch with programmatic stream serialization (WB200_NO_PDL=1 switches it off)
+
+struct WsPlan {
+    int tiles, split, kb_total, kb_per_split, stages, n_pad, smem;
+    uint32_t tmem_cols;
+};
+
+static WsPlan ws_plan(int n, int N_out, int K, int force_split /*0: auto*/) {
+    WsPlan p{};
+    p.tiles    = ceil_div(N_out, 128);
+    p.kb_total = ceil_div(K, 64);
+    p.n_pad    = (int) pad_to(std::max(n, 1), 16);
+    int split  = force_split;
+    if (split <= 0) {
+        // ~one CTA per SM, at least two k-blocks (32 KB of weights) per CTA
+        split = std::max(1, 148 / p.tiles);
+        split = std::min(split, std::max(1, p.kb_total / 2));
+    }
+    split          = std::min(split, p.kb_total);
+    p.kb_per_split = ceil_div(p.kb_total, split);
+    p.split        = ceil_div(p.kb_total, p.kb_per_split);
+    const int stage_bytes = WS_A_BYTES + p.n_pad * 128;
+    p.stages = std::max(1, std::min(std::min(8, p.kb_per_split), (100 * 1024) / stage_bytes));
+    p.smem   = p.stages * stage_bytes + 1024 + 256;
+    uint32_t c = 32;
+    while ((int) c < p.n_pad) c <<= 1;
+    p.tmem_cols = c;
+    return p;
+}
+
+template <typename... KArgs, typename... Args>
+static bool launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = (pdl && g_pdl) ? 1 : 0;
+    WB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
+    g_step_launches.fetch_add(1);
+    return true;
+}
+
+struct WsOut {
+    // mode 0
+    float * partial = nullptr;
+    // mode 1
+    void * out = nullptr;
+    int out_f16 = 0;
+    int64_t ldo = 0;
+    const float * bias = nullptr;
+    const __half * gelu_table = nullptr;
+};
+
+// X: f16 [n][K] row-major (ld = K); W: f16 [N_out][K].  Returns the split count through *split_out (mode 0).
+static bool gemm_wstream(const __half * W, const __half * X, int n, int N_out, int K, const WsOut & o, int force_split, int * split_out,
+                         cudaStream_t s, bool pdl) {
+    WB_CHECK(n >= 1 && n <= 256, "gemm_wstream handles 1..256 token rows (got %d)\n", n);
+    const bool direct = o.out != nullptr;
+    WsPlan p = ws_plan(n, N_out, K, direct ? 1 : force_split);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WB_CUDA_OK(cudaFuncSetAttribute(gemm_wstream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+        attr_set = true;
+    }
+    CUtensorMap tw, tx;
+    if (!tmap_encode_2d(&tw, W, (uint64_t) K, (uint64_t) N_out, (uint64_t) K, 64, 128)) return false;
+    if (!tmap_encode_2d(&tx, X, (uint64_t) K, (uint64_t) n, (uint64_t) K, 64, (uint32_t) p.n_pad)) return false;
+    WsArgs a{};
+    a.n = n; a.n_pad = p.n_pad; a.N_out = N_out;
+    a.kb_total = p.kb_total; a.kb_per_split = p.kb_per_split; a.stages = p.stages;
+    a.mode = direct ? 1 : 0;
+    a.partial = o.partial; a.split_stride = (int64_t) n * N_out;
+    a.out = o.out; a.out_f16 = o.out_f16; a.ldo = o.ldo; a.bias = o.bias; a.gelu_table = o.gelu_table;
+    a.tmem_cols = p.tmem_cols;
+    if (split_out) *split_out = p.split;
+    return launch_k(gemm_wstream_kernel, dim3(p.tiles, p.split), dim3(WS_THREADS), (size_t) p.smem, s, pdl, tw, tx, a);
+}
+
+// =============================================================================================
+// ln_reduce: x = [residual | embedding] (+ bias + sum of split-K partials);  xa = f16(LayerNorm(x) * gamma + beta)
+// =============================================================================================
+// One CTA per token row.  The split partials are summed in split order (deterministic); then (acc + bias) + residual
+// as the reference's ggml_add chain (whisper.cpp:2216-2220, 2251-2254); LayerNorm as ggml_norm (ops.cpp:3199-3248:
+// mean and variance accumulated in double) followed by the separate f32 mul / add with gamma / beta (wc:2121-2126).
+struct LnArgs {
+    const float * partial;  // [split][n][S] or null
+    int split;
+    int64_t split_stride;
+    const float * bias;     // [S] (with partial)
+    const float * res;      // [n][S] residual stream in (null with embed)
+    const __half * te;      // embedding mode: x = f32(te[token]) + pe[pos]  (wc:2531-2534)
+    const float * pe;
+    const int * tokens;
+    const int * pos;
+    float * x_out;          // [n][S] residual stream out (may alias res)
+    __half * xa_out;        // [n][S] LayerNorm output, f16
+    const float * gamma;
+    const float * beta;
+    float eps;
+    int S;
+};
+
+static constexpr int LN_THREADS = 256;
+static constexpr int LN_MAX_PER_THREAD = 8;  // S <= 2048
+
+__device__ __forceinline__ double block_sum_double(double v, double * red /*[8]*/) {
+    v = warp_sum_d(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double r = 0.0;
+#pragma unroll
+    for (int w = 0; w < LN_THREADS / 32; ++w) r += red[w];
+    return r;
+}
+
+__global__ void __launch_bounds__(LN_THREADS)
+ln_reduce_kernel(LnArgs a) {
+    __shared__ double red[8];
+    pdl_launch_dependents();
+    pdl_wait();
+    const int row = blockIdx.x, tid = threadIdx.x, S = a.S;
+    float v[LN_MAX_PER_THREAD];
+    double sum = 0.0;
+#pragma unroll
+    for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
+        const int i = tid + q * LN_THREADS;
+        float x = 0.0f;
+        if (i < S) {
+            if (a.te != nullptr) x = __fadd_rn(__half2float(a.te[(int64_t) a.tokens[row] * S + i]), a.pe[(int64_t) a.pos[row] * S + i]);
+            else x = a.res[(int64_t) row * S + i];
+            if (a.partial != nullptr) {
+                const float * p = a.partial + (int64_t) row * S + i;
+                float acc = p[0];
+                for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
+                acc = __fadd_rn(acc, __ldg(a.bias + i));
+                x = __fadd_rn(acc, x);
+            }
+            a.x_out[(int64_t) row * S + i] = x;
+            sum += (double) x;
+        }
+        v[q] = x;
+    }
+    sum = block_sum_double(sum, red);
+    const float mean = (float) (sum / S);
+    double sum2 = 0.0;
+#pragma unroll
+    for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
+        const int i = tid + q * LN_THREADS;
+        if (i < S) {
+            v[q] = __fsub_rn(v[q], mean);
+            sum2 += (double) __fmul_rn(v[q], v[q]);
+        }
+    }
+    sum2 = block_sum_double(sum2, red);
+    const float variance = (float) (sum2 / S);
+    const float scale = __frcp_rn(__fsqrt_rn(__fadd_rn(variance, a.eps)));
+#pragma unroll
+    for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
+        const int i = tid + q * LN_THREADS;
+        if (i < S) {
+            const float y = __fadd_rn(__fmul_rn(__fmul_rn(v[q], scale), __ldg(a.gamma + i)), __ldg(a.beta + i));
+            a.xa_out[(int64_t) row * S + i] = __float2half_rn(y);
+        }
+    }
+}
+
+// =============================================================================================
+// self_attn_step: finish this row's Q/K/V head slice from the QKV split-K partials, append K/V to the cache, attend
+// =============================================================================================
+// grid (H, n), 128 threads.  Q and K carry the D^-1/4 scale (wc:2522,2566,2573), bias then scale; Q, K, V and the
+// softmax probabilities are rounded to f16 where the reference's mul_mat converts them.
+struct SelfArgs {
+    const float * partial;  // [split][n][3S]
+    int split;
+    int64_t split_stride;
+    const float * bias;     // [3S] = (bq, 0, bv)
+    float scale;
+    const SelfKvRow * rows;
+    int S, layer;
+    __half * out;           // [n][S]
+};
+
+__global__ void __launch_bounds__(128)
+self_attn_step_kernel(SelfArgs a) {
+    extern __shared__ float s_sc[];
+    __shared__ float s_q[64];
+    __shared__ float s_red[4];
+    __shared__ double s_redd[4];
+    __shared__ float s_acc[2][64];
+    pdl_launch_dependents();
+    pdl_wait();
+    const int h = blockIdx.x, j = blockIdx.y, tid = threadIdx.x, S = a.S;
+    const SelfKvRow r = a.rows[j];
+    __half * kb = r.k_base + (int64_t) a.layer * r.n_ctx * S + h * 64;
+    __half * vb = r.v_base + (int64_t) a.layer * r.n_ctx * S + h * 64;
+    for (int t = tid; t < 192; t += 128) {
+        const int part = t >> 6, d = t & 63, col = part * S + h * 64 + d;
+        const float * p = a.partial + (int64_t) j * 3 * S + col;
+        float acc = p[0];
+        for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
+        acc = __fadd_rn(acc, __ldg(a.bias + col));
+        if (part < 2) acc = __fmul_rn(acc, a.scale);
+        const __half hv = __float2half_rn(acc);
+        if (part == 0) s_q[d] = __half2float(hv);
+        else if (part == 1) kb[(int64_t) r.store_cell * S + d] = hv;
+        else vb[(int64_t) r.store_cell * S + d] = hv;
+    }
+    __syncthreads();  // orders this CTA's K/V stores before its own loads below
+
+    const int n = r.n_cells;
+    float mx = -INFINITY;
+    for (int c = tid; c < n; c += 128) {
+        const int cell = r.cells ? r.cells[c] : c;
+        const uint4 * kr = (const uint4 *) (kb + (int64_t) cell * S);
+        float acc = 0.0f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const uint4 u = kr[q];
+            const __half2 * hp = (const __half2 *) &u;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(hp[e]);
+                acc = fmaf(f.x, s_q[q * 8 + e * 2], acc);
+                acc = fmaf(f.y, s_q[q * 8 + e * 2 + 1], acc);
+            }
+        }
+        s_sc[c] = acc;
+        mx = fmaxf(mx, acc);
+    }
+    mx = warp_max(mx);
+    if ((tid & 31) == 0) s_red[tid >> 5] = mx;
+    __syncthreads();
+    mx = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+    double sum = 0.0;
+    for (int c = tid; c < n; c += 128) {
+        const float e = expf(__fsub_rn(s_sc[c], mx));
+        s_sc[c] = e;
+        sum += (double) e;
+    }
+    sum = warp_sum_d(sum);
+    if ((tid & 31) == 0) s_redd[tid >> 5] = sum;
+    __syncthreads();
+    sum = s_redd[0] + s_redd[1] + s_redd[2] + s_redd[3];
+    const float inv = (float) (1.0 / sum);
+    for (int c = tid; c < n; c += 128) s_sc[c] = __half2float(__float2half_rn(__fmul_rn(s_sc[c], inv)));
+    __syncthreads();
+    const int d = tid & 63, half = tid >> 6;
+    float acc = 0.0f;
+    for (int c = half; c < n; c += 2) {
+        const int cell = r.cells ? r.cells[c] : c;
+        acc = fmaf(s_sc[c], __half2float(vb[(int64_t) cell * S + d]), acc);
+    }
+    s_acc[half][d] = acc;
+    __syncthreads();
+    if (tid < 64) a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(s_acc[0][tid] + s_acc[1][tid]);
+}
+
+// =============================================================================================
+// cross_attn_step: the kernel that bounds batched decoding (2 * T * 64 * 2 B of K/V per row, head and layer)
+// =============================================================================================
+// grid (H, n).  8 consumer warps + 1 producer warp.  The producer streams the contiguous K panel [T][64] f16 and then
+// the V panel of this (state, layer, head) in 16 KB chunks (128 keys) with cp.async.bulk into an mbarrier ring
+// (L2 evict-first: every byte is used once per step); consumers compute scores from shared memory, the
+// row softmax (max, exp, double sum, 1/sum: ggml_soft_max_ext, ops.cpp:4731-4827; scale applied to K.Q as wc:2732-2734),
+// round P to f16 (mul_mat src1 conversion) and accumulate P.V in f32.  Q is finished from the cross-Q split-K partials.
+struct CrossArgs {
+    const float * partial;  // [split][n][S] cross-Q partials
+    int split;
+    int64_t split_stride;
+    const float * bias;     // [S]
+    const __half * q_f16;   // alternative to partial: finished Q [n][S] (tests)
+    const CrossKvRow * rows;
+    int H, T, S, layer;
+    float scale;
+    __half * out;           // [n][S]
+    int stages;
+};
+
+static constexpr int XS_CONSUMERS  = 256;
+static constexpr int XS_THREADS    = XS_CONSUMERS + 32;
+static constexpr int XS_CHUNK_ROWS = 128;
+static constexpr int XS_CHUNK_BYTES = XS_CHUNK_ROWS * 128;
+
+__global__ void __launch_bounds__(XS_THREADS, 2)
+cross_attn_step_kernel(CrossArgs a) {
+    extern __shared__ uint8_t xs_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) xs_raw + 127) & ~(uintptr_t) 127);
+    uint8_t * ring   = smem;
+    float * s_sc     = (float *) (ring + a.stages * XS_CHUNK_BYTES);          // [T] scores / probabilities
+    uint64_t * full  = (uint64_t *) (s_sc + ((a.T + 31) & ~31));
+    uint64_t * empty = full + a.stages;
+    __shared__ float s_q[64];
+    __shared__ float s_red[8];
+    __shared__ double s_redd[8];
+    __shared__ float s_acc[8][4][64];
+
+    const int h = blockIdx.x, j = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int T = a.T, S = a.S;
+    const int nck = (T + XS_CHUNK_ROWS - 1) / XS_CHUNK_ROWS;  // chunks per panel
+    if (tid == 0) {
+        for (int s = 0; s < a.stages; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, 8);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+    pdl_wait();
+    const CrossKvRow r = a.rows[j];
+
+    if (warp == 8) {
+        // ---------------- producer ----------------
+        if (lane == 0) {
+            const uint64_t pol = l2_policy_evict_first();
+            const __half * kp = r.kv_base + ((int64_t) a.layer * 2 * a.H + h) * (int64_t) T * 64;
+            const __half * vp = r.kv_base + ((int64_t) a.layer * 2 * a.H + a.H + h) * (int64_t) T * 64;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int c = 0; c < 2 * nck; ++c) {
+                const int ci = c < nck ? c : c - nck;
+                const int rows = min(XS_CHUNK_ROWS, T - ci * XS_CHUNK_ROWS);
+                const __half * src = (c < nck ? kp : vp) + (int64_t) ci * XS_CHUNK_ROWS * 64;
+                mbar_wait(empty + stage, phase ^ 1);
+                mbar_expect_tx(full + stage, (uint32_t) rows * 128);
+                bulk_load_1d_hint(ring + stage * XS_CHUNK_BYTES, src, (uint32_t) rows * 128, full + stage, pol);
+                if (++stage == a.stages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers (warps 0..7) ----------------
+    if (tid < 64) {
+        float qv;
+        if (a.q_f16 != nullptr) {
+            qv = __half2float(a.q_f16[(int64_t) j * S + h * 64 + tid]);
+        } else {
+            const float * p = a.partial + (int64_t) j * S + h * 64 + tid;
+            float acc = p[0];
+            for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
+            acc = __fadd_rn(acc, __ldg(a.bias + h * 64 + tid));
+            qv = __half2float(__float2half_rn(acc));
+        }
+        s_q[tid] = qv;
+    }
+    named_bar_sync(1, XS_CONSUMERS);
+
+    const int sub = lane & 7, kq = lane >> 3;
+    float qf[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) qf[e] = s_q[sub * 8 + e];
+
+    int stage = 0;
+    uint32_t phase = 0;
+    float mx = -INFINITY;
+    for (int c = 0; c < nck; ++c) {
+        const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
+        mbar_wait(full + stage, phase);
+        const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
+#pragma unroll
+        for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
+            const int rr = it * 32 + warp * 4 + kq;
+            float acc = 0.0f;
+            if (rr < rows) {
+                const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
+                const __half2 * hp = (const __half2 *) &u;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = __half22float2(hp[e]);
+                    acc = fmaf(f.x, qf[e * 2], acc);
+                    acc = fmaf(f.y, qf[e * 2 + 1], acc);
+                }
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (rr < rows && sub == 0) {
+                const float sc = __fmul_rn(acc, a.scale);
+                s_sc[c * XS_CHUNK_ROWS + rr] = sc;
+                mx = fmaxf(mx, sc);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + stage);
+        if (++stage == a.stages) {
+            stage = 0;
+            phase ^= 1;
+        }
+    }
+    mx = warp_max(mx);
+    if (lane == 0) s_red[warp] = mx;
+    named_bar_sync(1, XS_CONSUMERS);
+    mx = s_red[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) mx = fmaxf(mx, s_red[w]);
+    double sum = 0.0;
+    for (int t = tid; t < T; t += XS_CONSUMERS) {
+        const float e = expf(__fsub_rn(s_sc[t], mx));
+        s_sc[t] = e;
+        sum += (double) e;
+    }
+    sum = warp_sum_d(sum);
+    if (lane == 0) s_redd[warp] = sum;
+    named_bar_sync(1, XS_CONSUMERS);
+    sum = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) sum += s_redd[w];
+    const float inv = (float) (1.0 / sum);
+    for (int t = tid; t < T; t += XS_CONSUMERS) s_sc[t] = __half2float(__float2half_rn(__fmul_rn(s_sc[t], inv)));
+    named_bar_sync(1, XS_CONSUMERS);
+
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
+    for (int c = 0; c < nck; ++c) {
+        const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
+        mbar_wait(full + stage, phase);
+        const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
+#pragma unroll
+        for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
+            const int rr = it * 32 + warp * 4 + kq;
+            if (rr < rows) {
+                const float p = s_sc[c * XS_CHUNK_ROWS + rr];
+                const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
+                const __half2 * hp = (const __half2 *) &u;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = __half22float2(hp[e]);
+                    acc[e * 2]     = fmaf(p, f.x, acc[e * 2]);
+                    acc[e * 2 + 1] = fmaf(p, f.y, acc[e * 2 + 1]);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + stage);
+        if (++stage == a.stages) {
+            stage = 0;
+            phase ^= 1;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s_acc[warp][kq][sub * 8 + e] = acc[e];
+    named_bar_sync(1, XS_CONSUMERS);
+    if (tid < 64) {
+        float o = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w)
+#pragma unroll
+            for (int g = 0; g < 4; ++g) o += s_acc[w][g][tid];
+        a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
+    }
+}
+
+static int xs_smem_bytes(int T, int stages) { return stages * XS_CHUNK_BYTES + ((T + 31) & ~31) * 4 + 2 * stages * 8 + 128 + 64; }
+
+// =============================================================================================
+// the step graph
+// =============================================================================================
+namespace {
+
+struct GraphEntry {
+    cudaGraphExec_t exec = nullptr;
+    uint64_t launches = 0;
+};
+
+struct StepWs {
+    int cap_n = 0;
+    uint8_t * base = nullptr;
+    float * x = nullptr;         // [n][S] residual stream
+    __half * xa = nullptr;       // [n][S] LayerNorm output
+    __half * att = nullptr;      // [n][S] attention output
+    __half * hb = nullptr;       // [n][4S]
+    float * partial = nullptr;   // split-K partial sums
+    float * logits = nullptr;    // [n][V]
+    float * samp_work = nullptr; // [n][3][V]
+    uint8_t * h_stage = nullptr; // pinned
+    uint8_t * d_stage = nullptr;
+    size_t stage_bytes = 0;
+    SamplerOut * h_out = nullptr;  // pinned
+    SamplerOut * d_out = nullptr;
+    std::map<uint64_t, GraphEntry> graphs;
+};
+
+struct StageLayout {
+    size_t o_tok, o_pos, o_self, o_cross, o_samp, bytes;
+};
+static StageLayout stage_layout(int n) {
+    StageLayout L{};
+    size_t off = 0;
+    auto sub = [&](size_t b) {
+        const size_t o = off;
+        off += (b + 15) & ~(size_t) 15;
+        return o;
+    };
+    L.o_tok = sub((size_t) n * 4);
+    L.o_pos = sub((size_t) n * 4);
+    L.o_self = sub((size_t) n * sizeof(SelfKvRow));
+    L.o_cross = sub((size_t) n * sizeof(CrossKvRow));
+    L.o_samp = sub((size_t) n * sizeof(SamplerRow));
+    L.bytes = off;
+    return L;
+}
+
+void destroy_graphs(StepWs & ws) {
+    for (auto & kv : ws.graphs)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    ws.graphs.clear();
+}
+
+void free_ws(StepWs & ws) {
+    destroy_graphs(ws);
+    cudaFree(ws.base);
+    cudaFree(ws.d_stage);
+    cudaFree(ws.d_out);
+    if (ws.h_stage) cudaFreeHost(ws.h_stage);
+    if (ws.h_out) cudaFreeHost(ws.h_out);
+    ws = StepWs();
+}
+
+bool ensure_ws(Context & ctx, StepWs & ws, int n) {
+    if (ws.base && ws.cap_n >= n) return true;
+    const auto & hp = ctx.model.hp;
+    const int S = hp.n_text_state, V = hp.n_vocab;
+    const int cap = std::min(256, std::max(n, std::max(16, ws.cap_n * 2)));
+    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    free_ws(ws);  // graphs bake the workspace pointers
+    size_t max_part = 0;
+    const int shapes[4][2] = {{3 * S, S}, {S, S}, {S, 4 * S}, {4 * S, S}};
+    for (auto & sh : shapes) {
+        const WsPlan p = ws_plan(cap, sh[0], sh[1], 0);
+        max_part = std::max(max_part, (size_t) p.split * cap * sh[0]);
+    }
+    size_t off = 0;
+    auto take = [&](size_t b) {
+        const size_t o = off;
+        off += (b + 1023) & ~(size_t) 1023;
+        return o;
+    };
+    const size_t o_x = take((size_t) cap * S * 4), o_xa = take((size_t) cap * S * 2), o_att = take((size_t) cap * S * 2);
+    const size_t o_hb = take((size_t) cap * 4 * S * 2), o_part = take(max_part * 4), o_lg = take((size_t) cap * V * 4);
+    const size_t o_sw = take((size_t) cap * 3 * V * 4);
+    WB_CUDA_OK(cudaMalloc((void **) &ws.base, off));
+    ws.x = (float *) (ws.base + o_x); ws.xa = (__half *) (ws.base + o_xa); ws.att = (__half *) (ws.base + o_att);
+    ws.hb = (__half *) (ws.base + o_hb); ws.partial = (float *) (ws.base + o_part); ws.logits = (float *) (ws.base + o_lg);
+    ws.samp_work = (float *) (ws.base + o_sw);
+    ws.stage_bytes = stage_layout(cap).bytes;
+    WB_CUDA_OK(cudaMallocHost((void **) &ws.h_stage, ws.stage_bytes));
+    WB_CUDA_OK(cudaMalloc((void **) &ws.d_stage, ws.stage_bytes));
+    WB_CUDA_OK(cudaMallocHost((void **) &ws.h_out, (size_t) cap * sizeof(SamplerOut)));
+    WB_CUDA_OK(cudaMalloc((void **) &ws.d_out, (size_t) cap * sizeof(SamplerOut)));
+    ws.cap_n = cap;
+    return true;
+}
+
+// issues every launch of one decode step for n rows on `s` (live or under stream capture)
+bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & sst, cudaStream_t s) {
+    const Model & m = ctx.model;
+    const auto & hp = m.hp;
+    const int S = hp.n_text_state, H = hp.n_text_head, L = hp.n_text_layer, V = hp.n_vocab;
+    const StageLayout SL = stage_layout(n);
+    const int * d_tok = (const int *) (ws.d_stage + SL.o_tok);
+    const int * d_pos = (const int *) (ws.d_stage + SL.o_pos);
+    const SelfKvRow * d_self = (const SelfKvRow *) (ws.d_stage + SL.o_self);
+    const CrossKvRow * d_cross = (const CrossKvRow *) (ws.d_stage + SL.o_cross);
+    const SamplerRow * d_samp = (const SamplerRow *) (ws.d_stage + SL.o_samp);
+    const float kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
+    static bool attrs = false;
+    const int xs_stages = 5;
+    if (!attrs) {
+        WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        WB_CUDA_OK(cudaFuncSetAttribute(self_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5120 * 4));
+        attrs = true;
+    }
+    WB_CHECK(S <= LN_THREADS * LN_MAX_PER_THREAD && (S % 64) == 0, "unsupported text state %d\n", S);
+    WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage, ws.h_stage, SL.bytes, cudaMemcpyHostToDevice, s));
+
+    auto ln = [&](const float * partial, int split, const float * bias, bool embed, const Norm & nm) {
+        LnArgs a{};
+        a.partial = partial; a.split = split; a.split_stride = (int64_t) n * S; a.bias = bias;
+        a.res = embed ? nullptr : ws.x;
+        a.te = embed ? m.d_te : nullptr; a.pe = m.d_pe; a.tokens = d_tok; a.pos = d_pos;
+        a.x_out = ws.x; a.xa_out = ws.xa; a.gamma = nm.g; a.beta = nm.b; a.eps = hp.eps; a.S = S;
+        return launch_k(ln_reduce_kernel, dim3(n), dim3(LN_THREADS), 0, s, !embed, a);
+    };
+    if (!ln(nullptr, 0, nullptr, true, L > 0 ? m.dec[0].ln1 : m.d_ln)) return false;
+    for (int il = 0; il < L; ++il) {
+        const DecLayer & l = m.dec[il];
+        int split = 1;
+        WsOut po{};
+        po.partial = ws.partial;
+        if (!gemm_wstream(l.qkv.w, ws.xa, n, 3 * S, S, po, 0, &split, s, true)) return false;
+        {
+            SelfArgs a{};
+            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * 3 * S; a.bias = l.qkv.b; a.scale = kq_scale;
+            a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
+            if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), (size_t) 5120 * 4, s, true, a)) return false;
+        }
+        if (!gemm_wstream(l.o.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
+        if (!ln(ws.partial, split, l.o.b, false, l.lnc)) return false;
+        if (!gemm_wstream(l.cq.w, ws.xa, n, S, S, po, 0, &split, s, true)) return false;
+        {
+            CrossArgs a{};
+            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * S; a.bias = l.cq.b; a.q_f16 = nullptr;
+            a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att; a.stages = xs_stages;
+            if (!launch_k(cross_attn_step_kernel, dim3(H, n), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, xs_stages), s, true, a)) return false;
+        }
+        if (!gemm_wstream(l.co.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
+        if (!ln(ws.partial, split, l.co.b, false, l.ln2)) return false;
+        {
+            WsOut d{};
+            d.out = ws.hb; d.out_f16 = 1; d.ldo = 4 * S; d.bias = l.fc1.b; d.gelu_table = m.gelu_table;
+            if (!gemm_wstream(l.fc1.w, ws.xa, n, 4 * S, S, d, 1, nullptr, s, true)) return false;
+        }
+        if (!gemm_wstream(l.fc2.w, ws.hb, n, S, 4 * S, po, 0, &split, s, true)) return false;
+        if (!ln(ws.partial, split, l.fc2.b, false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln)) return false;
+    }
+    {   // tied-embedding logits (wc:2835)
+        WsOut d{};
+        d.out = ws.logits; d.out_f16 = 0; d.ldo = V;
+        if (!gemm_wstream(m.d_te, ws.xa, n, V, S, d, 1, nullptr, s, true)) return false;
+    }
+    if (!sample_rows(sst, ws.logits, V, d_samp, n, ws.samp_work, ws.d_out, s)) return false;
+    WB_CUDA_OK(cudaMemcpyAsync(ws.h_out, ws.d_out, (size_t) n * sizeof(SamplerOut), cudaMemcpyDeviceToHost, s));
+    return true;
+}
+
+}  // namespace
+
+static StepWs * step_ws(Context & ctx) {
+    if (!ctx.step) ctx.step = new StepWs();
+    return (StepWs *) ctx.step;
+}
+
+void step_release(Context & ctx) {
+    if (!ctx.step) return;
+    StepWs * ws = (StepWs *) ctx.step;
+    free_ws(*ws);
+    delete ws;
+    ctx.step = nullptr;
+}
+
+bool step_eligible(const Context & ctx, const BatchRow * rows, int n, bool any_host_dists) {
+    static const bool disabled = getenv("WB200_NO_STEP_GRAPH") != nullptr;
+    if (disabled || any_host_dists || n < 1 || n > 256 || ctx.model.n_loaded == 0 || ctx.model.hp.n_text_layer < 1) return false;
+    const int S = ctx.model.hp.n_text_state;
+    if (S > LN_THREADS * LN_MAX_PER_THREAD || (S % 64) != 0) return false;
+    const int T = rows[0].st->cross_T;
+    if (T <= 0) return false;
+    for (int i = 0; i < n; ++i) {
+        const BatchRow & r = rows[i];
+        if (!r.want_logits || r.seq_id != 0 || r.st->cross_T != T) return false;
+        for (int k = 0; k < i; ++k)
+            if (rows[k].st == r.st) return false;  // one row per state
+        // the cache must be in append order: cells [0, used) live for sequence 0 at earlier positions, everything after free
+        const KvCache & kv = r.st->kv_self;
+        int used = 0;
+        while (used < kv.size && kv.cells[(size_t) used].pos >= 0) {
+            if (!kv.cells[(size_t) used].has(0) || kv.cells[(size_t) used].pos > r.pos) return false;
+            ++used;
+        }
+        if (used >= kv.size || used > 5000) return false;
+        for (int c = used + 1; c < kv.size; ++c)
+            if (kv.cells[(size_t) c].pos >= 0) return false;
+    }
+    return true;
+}
+
+bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows, Decoder ** decs) {
+    WB_CUDA_OK(cudaSetDevice(ctx.model.device));
+    const int64_t t0 = time_us();
+    static const bool no_graph = getenv("WB200_STEP_NO_GRAPH") != nullptr;
+    g_pdl = getenv("WB200_NO_PDL") == nullptr;
+    StepWs & ws = *step_ws(ctx);
+    if (!ensure_ws(ctx, ws, n)) return false;
+    const int T = rows[0].st->cross_T;
+    const StageLayout SL = stage_layout(n);
+    int * h_tok = (int *) (ws.h_stage + SL.o_tok);
+    int * h_pos = (int *) (ws.h_stage + SL.o_pos);
+    SelfKvRow * h_self = (SelfKvRow *) (ws.h_stage + SL.o_self);
+    CrossKvRow * h_cross = (CrossKvRow *) (ws.h_stage + SL.o_cross);
+    SamplerRow * h_samp = (SamplerRow *) (ws.h_stage + SL.o_samp);
+    for (int i = 0; i < n; ++i) {
+        State * st = rows[i].st;
+        KvCache & kv = st->kv_self;
+        if (!kv.find_slot(&rows[i].pos, &rows[i].seq_id, 1)) {  // wc:2885-2897
+            log_error("%s: failed to find a KV slot\n", __func__);
+            return false;
+        }
+        kv.n = std::min(kv.size, std::max(1, kv.cell_max()));
+        h_tok[i] = rows[i].token;
+        h_pos[i] = rows[i].pos;
+        SelfKvRow & sr = h_self[i];
+        sr.k_base = kv.k; sr.v_base = kv.v; sr.cells = nullptr;
+        sr.n_cells = kv.head + 1; sr.store_cell = kv.head; sr.n_ctx = kv.size;
+        h_cross[i] = CrossKvRow{st->kv_cross, nullptr, 0, 0};
+        h_samp[i] = srows[i];
+        h_samp[i].logits_row = i;
+        h_samp[i].work_slot = i;
+    }
+    cudaStream_t s = ctx.stream;
+    if (no_graph) {
+        if (!issue_step(ctx, ws, n, T, sst, s)) return false;
+    } else {
+        const uint64_t key = ((uint64_t) n << 32) | (uint32_t) T;
+        auto it = ws.graphs.find(key);
+        if (it == ws.graphs.end()) {
+            const uint64_t l0 = g_step_launches.load() + kernel_launch_count();
+            cudaGraph_t graph = nullptr;
+            prof_suspend(true);
+            WB_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+            const bool ok = issue_step(ctx, ws, n, T, sst, s);
+            const cudaError_t e = cudaStreamEndCapture(s, &graph);
+            prof_suspend(false);
+            if (!ok || e != cudaSuccess || graph == nullptr) {
+                if (graph) cudaGraphDestroy(graph);
+                log_error("%s: capturing the decode-step graph failed (%s)\n", __func__, cudaGetErrorString(e));
+                return false;
+            }
+            GraphEntry ge;
+            ge.launches = g_step_launches.load() + kernel_launch_count() - l0;
+            const cudaError_t ei = cudaGraphInstantiate(&ge.exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ei != cudaSuccess) {
+                log_error("%s: cudaGraphInstantiate failed (%s)\n", __func__, cudaGetErrorString(ei));
+                return false;
+            }
+            // launches counted while capturing were not executed
+            g_step_launches.fetch_sub(ge.launches - 1);
+            it = ws.graphs.emplace(key, ge).first;
+        }
+        WB_CUDA_OK(cudaGraphLaunch(it->second.exec, s));
+        g_step_launches.fetch_add(it->second.launches);
+    }
+    WB_CUDA_OK(cudaStreamSynchronize(s));
+    for (int i = 0; i < n; ++i)
+        if (decs && decs[i]) decs[i]->picked = ws.h_out[i];
+    const int64_t dt = time_us() - t0;
+    for (int i = 0; i < n; ++i) {  // wc:2982-2991: single-token decodes
+        rows[i].st->t_decode_us += dt / n;
+        rows[i].st->n_decode++;
+    }
+    return true;
+}
+
+uint64_t step_launch_count() { return g_step_launches.load(); }
+
+// =============================================================================================
+// test / micro-benchmark hooks
+// =============================================================================================
+bool test_gemm_wstream(const __half * w, const __half * x, float * out, int n, int N_out, int K, const float * bias, int force_split) {
+    g_pdl = false;
+    if (force_split == 1) {
+        WsOut d{};
+        d.out = out; d.out_f16 = 0; d.ldo = N_out; d.bias = bias;
+        if (!gemm_wstream(w, x, n, N_out, K, d, 1, nullptr, 0, false)) return false;
+        WB_CUDA_OK(cudaDeviceSynchronize());
+        return true;
+    }
+    // partial mode: reduce on the host side of the test through a plain device loop (ln_reduce needs LayerNorm weights)
+    const WsPlan p = ws_plan(n, N_out, K, force_split);
+    float * part = nullptr;
+    WB_CUDA_OK(cudaMalloc((void **) &part, (size_t) p.split * n * N_out * 4));
+    WsOut po{};
+    po.partial = part;
+    int split = 0;
+    bool ok = gemm_wstream(w, x, n, N_out, K, po, force_split, &split, 0, false);
+    std::vector<float> h((size_t) split * n * N_out), o((size_t) n * N_out, 0.0f), hb;
+    ok = ok && cudaMemcpy(h.data(), part, h.size() * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    if (ok && bias) {
+        hb.resize((size_t) N_out);
+        ok = cudaMemcpy(hb.data(), bias, hb.size() * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    }
+    if (ok) {
+        for (size_t i = 0; i < o.size(); ++i) {
+            float acc = h[i];
+            for (int s = 1; s < split; ++s) acc += h[(size_t) s * n * N_out + i];
+            if (bias) acc += hb[i % (size_t) N_out];
+            o[i] = acc;
+        }
+        ok = cudaMemcpy(out, o.data(), o.size() * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    }
+    cudaFree(part);
+    return ok;
+}
+
+static bool launch_cross_test(const __half * q, const CrossKvRow * d_rows, __half * out, int n_rows, int H, int T, int layer, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) {
+        WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        attr = true;
+    }
+    CrossArgs a{};
+    a.q_f16 = q; a.rows = d_rows; a.H = H; a.T = T; a.S = H * 64; a.layer = layer; a.scale = (float) pow(64.0, -0.25); a.out = out; a.stages = 5;
+    return launch_k(cross_attn_step_kernel, dim3(H, n_rows), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, 5), s, false, a);
+}
+
+bool test_cross_attn_step(const __half * q_f16, const __half * kv, __half * out, int n_rows, int H, int T) {
+    std::vector<CrossKvRow> h((size_t) n_rows, CrossKvRow{kv, nullptr, 0, 0});
+    CrossKvRow * d_rows = nullptr;
+    WB_CUDA_OK(cudaMalloc((void **) &d_rows, h.size() * sizeof(CrossKvRow)));
+    bool ok = cudaMemcpy(d_rows, h.data(), h.size() * sizeof(CrossKvRow), cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && launch_cross_test(q_f16, d_rows, out, n_rows, H, T, 0, 0);
+    ok = ok && cudaDeviceSynchronize() == cudaSuccess;
+    cudaFree(d_rows);
+    return ok;
+}
+
+// captures `issue` (launches on stream 0's replacement `s`) into a graph, replays it `iters` times between two events
+template <typename F>
+static bool time_graph(F issue, int iters, float * ms_out) {
+    cudaStream_t s = nullptr;
+    WB_CUDA_OK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    cudaGraph_t g = nullptr;
+    cudaGraphExec_t ge = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    bool ok = issue(s) && cudaStreamSynchronize(s) == cudaSuccess;  // warm-up, live
+    prof_suspend(true);
+    ok = ok && cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+    ok = ok && issue(s);
+    ok = (cudaStreamEndCapture(s, &g) == cudaSuccess) && ok && g != nullptr;
+    prof_suspend(false);
+    ok = ok && cudaGraphInstantiate(&ge, g, 0) == cudaSuccess;
+    ok = ok && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+    if (ok) {
+        ok = cudaGraphLaunch(ge, s) == cudaSuccess;
+        cudaEventRecord(e0, s);
+        for (int i = 0; i < iters && ok; ++i) ok = cudaGraphLaunch(ge, s) == cudaSuccess;
+        cudaEventRecord(e1, s);
+        ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
+        if (ok) cudaEventElapsedTime(ms_out, e0, e1);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (ge) cudaGraphExecDestroy(ge);
+    if (g) cudaGraphDestroy(g);
+    cudaStreamDestroy(s);
+    return ok;
+}
+
+// n_rows sequences with their own [layers][2H][T][64] cross caches (so the working set is n_rows*layers*2*H*T*128 B,
+// far beyond L2 for the bench shapes); one launch per layer, `iters` sweeps, timed with events on the launching stream.
+bool bench_cross_attn_step(int n_rows, int H, int T, int layers, int iters, StepBenchResult * out) {
+    const size_t per_row = (size_t) layers * 2 * H * T * 64;
+    __half *kv = nullptr, *q = nullptr, *o = nullptr;
+    CrossKvRow * d_rows = nullptr;
+    bool ok = cudaMalloc((void **) &kv, per_row * n_rows * 2) == cudaSuccess && cudaMalloc((void **) &q, (size_t) n_rows * H * 64 * 2) == cudaSuccess &&
+              cudaMalloc((void **) &o, (size_t) n_rows * H * 64 * 2) == cudaSuccess &&
+              cudaMalloc((void **) &d_rows, (size_t) n_rows * sizeof(CrossKvRow)) == cudaSuccess;
+    if (ok) {
+        cudaMemset(kv, 0x11, per_row * n_rows * 2);
+        cudaMemset(q, 0x11, (size_t) n_rows * H * 64 * 2);
+        std::vector<CrossKvRow> h((size_t) n_rows);
+        for (int i = 0; i < n_rows; ++i) h[(size_t) i] = CrossKvRow{kv + per_row * i, nullptr, 0, 0};
+        ok = cudaMemcpy(d_rows, h.data(), h.size() * sizeof(CrossKvRow), cudaMemcpyHostToDevice) == cudaSuccess;
+    }
+    if (ok) {
+        float ms = 0.0f;
+        ok = time_graph([&](cudaStream_t st) {
+            bool k = true;
+            for (int l = 0; l < layers && k; ++l) k = launch_cross_test(q, d_rows, o, n_rows, H, T, l, st);
+            return k;
+        }, iters, &ms);
+        out->launches = iters * layers;
+        out->us_per_launch = 1e3 * ms / std::max(1, out->launches);
+        out->bytes_per_launch = (double) n_rows * H * T * 64 * 2 * 2;
+    }
+    cudaFree(kv); cudaFree(q); cudaFree(o); cudaFree(d_rows);
+    return ok;
+}
+
+// `n_weights` distinct [N_out][K] matrices are streamed round-robin (choose n_weights*N_out*K*2 B > L2)
+bool bench_gemm_wstream(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out) {
+    g_pdl = getenv("WB200_NO_PDL") == nullptr;
+    __half *w = nullptr, *x = nullptr;
+    float * part = nullptr;
+    const size_t wsz = (size_t) N_out * K;
+    const WsPlan p = ws_plan(n_rows, N_out, K, 0);
+    bool ok = cudaMalloc((void **) &w, wsz * n_weights * 2) == cudaSuccess && cudaMalloc((void **) &x, (size_t) n_rows * K * 2) == cudaSuccess &&
+              cudaMalloc((void **) &part, (size_t) p.split * n_rows * N_out * 4) == cudaSuccess;
+    if (ok) {
+        cudaMemset(w, 0x11, wsz * n_weights * 2);
+        cudaMemset(x, 0x11, (size_t) n_rows * K * 2);
+    }
+    WsOut po{};
+    po.partial = part;
+    if (ok) {
+        float ms = 0.0f;
+        ok = time_graph([&](cudaStream_t st) {
+            bool k = true;
+            for (int i = 0; i < n_weights && k; ++i) k = gemm_wstream(w + wsz * i, x, n_rows, N_out, K, po, 0, nullptr, st, i > 0);
+            return k;
+        }, iters, &ms);
+        out->launches = iters * n_weights;
+        out->us_per_launch = 1e3 * ms / std::max(1, out->launches);
+        out->bytes_per_launch = (double) wsz * 2 + (double) n_rows * K * 2 + (double) p.split * n_rows * N_out * 4;
+    }
+    cudaFree(w); cudaFree(x); cudaFree(part);
+    return ok;
+}
+}  // namespace wb
