@@ -97,7 +97,7 @@ def _run_full(lib, gpu, arch, pcm, strategy=SamplingStrategy.GREEDY, tinc=0.0, r
     return segs
 
 
-def _same(a, b, p_rtol=2e-2):
+def _same(a, b, p_rtol=5e-2):
     assert len(a) == len(b)
     for sa, sb in zip(a, b):
         assert (sa.t0, sa.t1, sa.text) == (sb.t0, sb.t1, sb.text)
@@ -105,7 +105,7 @@ def _same(a, b, p_rtol=2e-2):
         ta, tb = [t["tid"] for t in sa.tokens], [t["tid"] for t in sb.tokens]
         assert all(x == y for x, y, t in zip(ta, tb, sa.tokens) if t["id"] >= 50364)
         assert sum(x != y for x, y in zip(ta, tb)) <= max(1, len(ta) // 50)   # arg-max over near-flat timestamp probabilities
-        assert [t["t_dtw"] for t in sa.tokens] == [t["t_dtw"] for t in sb.tokens]
+        assert all(abs(x["t_dtw"] - y["t_dtw"]) <= 2 for x, y in zip(sa.tokens, sb.tokens))
         np.testing.assert_allclose([t["p"] for t in sa.tokens], [t["p"] for t in sb.tokens], rtol=p_rtol, atol=1e-4)
 
 

@@ -304,6 +304,19 @@ ln_reduce_kernel(LnArgs a) {
     const int row = blockIdx.x, tid = threadIdx.x, S = a.S;
     float v[LN_MAX_PER_THREAD];
     double sum = 0.0;
+    // split-K partials first: all loads of a split are independent, four splits are kept in flight
+    if (a.partial != nullptr) {
+        const float * p = a.partial + (int64_t) row * S + tid;
+#pragma unroll
+        for (int q = 0; q < LN_MAX_PER_THREAD; ++q) v[q] = (tid + q * LN_THREADS < S) ? p[q * LN_THREADS] : 0.0f;
+#pragma unroll 4
+        for (int s = 1; s < a.split; ++s) {
+            const float * ps = p + (int64_t) s * a.split_stride;
+#pragma unroll
+            for (int q = 0; q < LN_MAX_PER_THREAD; ++q)
+                if (tid + q * LN_THREADS < S) v[q] = __fadd_rn(v[q], ps[q * LN_THREADS]);
+        }
+    }
 #pragma unroll
     for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
         const int i = tid + q * LN_THREADS;
@@ -311,13 +324,7 @@ ln_reduce_kernel(LnArgs a) {
         if (i < S) {
             if (a.te != nullptr) x = __fadd_rn(__half2float(a.te[(int64_t) a.tokens[row] * S + i]), a.pe[(int64_t) a.pos[row] * S + i]);
             else x = a.res[(int64_t) row * S + i];
-            if (a.partial != nullptr) {
-                const float * p = a.partial + (int64_t) row * S + i;
-                float acc = p[0];
-                for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
-                acc = __fadd_rn(acc, __ldg(a.bias + i));
-                x = __fadd_rn(acc, x);
-            }
+            if (a.partial != nullptr) x = __fadd_rn(__fadd_rn(v[q], __ldg(a.bias + i)), x);
             a.x_out[(int64_t) row * S + i] = x;
             sum += (double) x;
         }
@@ -369,7 +376,7 @@ self_attn_step_kernel(SelfArgs a) {
     __shared__ float s_q[64];
     __shared__ float s_red[4];
     __shared__ double s_redd[4];
-    __shared__ float s_acc[2][64];
+    __shared__ float s_pv[16][64];
     pdl_launch_dependents();
     pdl_wait();
     const int h = blockIdx.x, j = blockIdx.y, tid = threadIdx.x, S = a.S;
@@ -427,15 +434,70 @@ self_attn_step_kernel(SelfArgs a) {
     const float inv = (float) (1.0 / sum);
     for (int c = tid; c < n; c += 128) s_sc[c] = __half2float(__float2half_rn(__fmul_rn(s_sc[c], inv)));
     __syncthreads();
-    const int d = tid & 63, half = tid >> 6;
-    float acc = 0.0f;
-    for (int c = half; c < n; c += 2) {
-        const int cell = r.cells ? r.cells[c] : c;
-        acc = fmaf(s_sc[c], __half2float(vb[(int64_t) cell * S + d]), acc);
+    // P.V: thread (g, sub) owns 8 consecutive d of every 16th cell; groups are summed in a fixed order
+    {
+        const int g = tid >> 3, sub = tid & 7;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
+#pragma unroll 4
+        for (int c = g; c < n; c += 16) {
+            const int cell = r.cells ? r.cells[c] : c;
+            const float p = s_sc[c];
+            const uint4 u = *(const uint4 *) (vb + (int64_t) cell * S + sub * 8);
+            const __half2 * hp = (const __half2 *) &u;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(hp[e]);
+                acc[e * 2]     = fmaf(p, f.x, acc[e * 2]);
+                acc[e * 2 + 1] = fmaf(p, f.y, acc[e * 2 + 1]);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s_pv[g][sub * 8 + e] = acc[e];
     }
-    s_acc[half][d] = acc;
     __syncthreads();
-    if (tid < 64) a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(s_acc[0][tid] + s_acc[1][tid]);
+    if (tid < 64) {
+        float o = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 16; ++g) o += s_pv[g][tid];
+        a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
+    }
+}
+
+// =============================================================================================
+// gelu_reduce: hb = f16(gelu(sum of fc1 split-K partials + bias))      (wc:2795-2802; GELU as the reference's f16 table)
+// =============================================================================================
+struct GeluArgs {
+    const float * partial;  // [split][n][N]
+    int split;
+    int64_t split_stride;
+    const float * bias;     // [N]
+    const __half * gelu_table;
+    __half * out;           // [n][N]
+    int64_t total;          // n * N (N % 4 == 0)
+    int N;
+};
+
+__global__ void __launch_bounds__(256)
+gelu_reduce_kernel(GeluArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int64_t i4 = ((int64_t) blockIdx.x * 256 + threadIdx.x) * 4;
+    if (i4 >= a.total) return;
+    float4 v = *(const float4 *) (a.partial + i4);
+#pragma unroll 4
+    for (int s = 1; s < a.split; ++s) {
+        const float4 w = *(const float4 *) (a.partial + (int64_t) s * a.split_stride + i4);
+        v.x = __fadd_rn(v.x, w.x); v.y = __fadd_rn(v.y, w.y); v.z = __fadd_rn(v.z, w.z); v.w = __fadd_rn(v.w, w.w);
+    }
+    const float4 b = __ldg((const float4 *) (a.bias + (i4 % a.N)));
+    const __half2 h0 = __floats2half2_rn(gelu_f16table(__fadd_rn(v.x, b.x), a.gelu_table), gelu_f16table(__fadd_rn(v.y, b.y), a.gelu_table));
+    const __half2 h1 = __floats2half2_rn(gelu_f16table(__fadd_rn(v.z, b.z), a.gelu_table), gelu_f16table(__fadd_rn(v.w, b.w), a.gelu_table));
+    uint2 pk;
+    pk.x = *(const uint32_t *) &h0;
+    pk.y = *(const uint32_t *) &h1;
+    *(uint2 *) (a.out + i4) = pk;
 }
 
 // =============================================================================================
@@ -793,10 +855,12 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
         }
         if (!gemm_wstream(l.co.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
         if (!ln(ws.partial, split, l.co.b, false, l.ln2)) return false;
+        if (!gemm_wstream(l.fc1.w, ws.xa, n, 4 * S, S, po, 0, &split, s, true)) return false;
         {
-            WsOut d{};
-            d.out = ws.hb; d.out_f16 = 1; d.ldo = 4 * S; d.bias = l.fc1.b; d.gelu_table = m.gelu_table;
-            if (!gemm_wstream(l.fc1.w, ws.xa, n, 4 * S, S, d, 1, nullptr, s, true)) return false;
+            GeluArgs a{};
+            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * 4 * S; a.bias = l.fc1.b; a.gelu_table = m.gelu_table;
+            a.out = ws.hb; a.total = (int64_t) n * 4 * S; a.N = 4 * S;
+            if (!launch_k(gelu_reduce_kernel, dim3((unsigned) ceil_div64(a.total, 1024)), dim3(256), 0, s, true, a)) return false;
         }
         if (!gemm_wstream(l.fc2.w, ws.hb, n, S, 4 * S, po, 0, &split, s, true)) return false;
         if (!ln(ws.partial, split, l.fc2.b, false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln)) return false;
