@@ -51,6 +51,17 @@ WHISPER_API void whisper_b200_device_sync(struct whisper_context * ctx);
 /* C[m][n] (f32 or f16) = sum_k A[m][k] * B[n][k], f16 row-major operands, optional f32 bias[n]. Returns 0 on success. */
 WHISPER_API int whisper_b200_test_gemm(const void * a_f16, const void * b_f16, void * c, int m, int n, int k, int lda, int ldb, int ldc,
                                        int c_is_f16, const float * bias, int block_n);
+/* as whisper_b200_test_gemm; flags: 1 = accumulate (f32: c += A.B^T + bias, done by TMA reduce-add), 2 = per-head f16 panels
+ * c[n/64][m][64].  Synchronises the device before returning. */
+WHISPER_API int whisper_b200_test_gemm_ex(const void * a_f16, const void * b_f16, void * c, int m, int n, int k, int lda, int ldb, int ldc,
+                                          int c_is_f16, const float * bias, int block_n, int flags);
+/* encoder-GEMM micro-benchmark on scratch buffers (flags as above, 4 = with bias; block_n 0 = auto/persistent) */
+WHISPER_API int whisper_b200_bench_gemm(int m, int n, int k, int c_is_f16, int flags, int block_n, int n_weights, int iters,
+                                        double * us_per_launch);
+/* fused encoder self-attention softmax(Q K^T / 8) V on device buffers: q, k, v f16 [W][H][T][64], out f16 [W*T][H*64] */
+WHISPER_API int whisper_b200_test_enc_attn(const void * q_f16, const void * k_f16, const void * v_f16, void * out_f16, int n_windows, int n_head,
+                                           int n_ctx);
+WHISPER_API int whisper_b200_bench_enc_attn(int n_windows, int n_head, int n_ctx, int iters, double * us_per_launch);
 /* log-mel of device PCM -> device mel [n_mel][n_len] using the context's filterbank */
 WHISPER_API int whisper_b200_test_mel(struct whisper_context * ctx, const float * d_pcm, int n_samples, float * d_mel);
 /* the decode-step cross-attention kernel on device buffers: q f16 [n][S], kv f16 [2H][T][64] per row (same kv for all rows) */

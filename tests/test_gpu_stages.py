@@ -42,6 +42,57 @@ def test_gemm_tcgen05_vs_torch(prod_lib, m, n, k, bn):
     assert err < 2e-3 * max(1.0, ref.abs().max().item()), err
 
 
+# the persistent kernel (auto block_n, >= 148 tiles): TMA-store epilogue in row / per-head-panel layouts, f32 / f16,
+# ragged M and N tails, and the in-place residual  c += A.B^T + bias  through TMA reduce-add (wc:2216-2220)
+@pytest.mark.parametrize("m,n,k,f16,flags", [(12000, 1280, 1280, 0, 0), (12000, 1280, 1280, 0, 1), (6000, 2560, 1280, 1, 2),
+                                              (4500, 5120, 1280, 1, 0), (3000, 1280, 5120, 0, 1), (20000, 384, 384, 1, 0),
+                                              (19999, 392, 384, 0, 1), (9001, 1000, 192, 1, 0)])
+def test_gemm_persistent_vs_torch(prod_lib, m, n, k, f16, flags):
+    import torch
+    torch.manual_seed(m + n + k)
+    a = (torch.randn(m, k, device="cuda") * 0.5).half()
+    b = (torch.randn(n, k, device="cuda") * 0.5).half()
+    bias = torch.randn(n, device="cuda", dtype=torch.float32)
+    ref = a.float() @ b.float().T + bias
+    if flags & 1:
+        c = torch.randn(m, n, device="cuda", dtype=torch.float32)
+        ref = c + ref
+    else:
+        c = torch.full((m, n), float("nan"), device="cuda", dtype=torch.float16 if f16 else torch.float32)
+    torch.cuda.synchronize()
+    r = prod_lib.whisper_b200_test_gemm_ex(a.data_ptr(), b.data_ptr(), c.data_ptr(), m, n, k, k, k, n, f16, bias.data_ptr(), 0, flags)
+    assert r == 0
+    out = c.float()
+    if flags & 2:  # [n/64][m][64] panels -> [m][n]
+        out = c.view(n // 64, m, 64).permute(1, 0, 2).reshape(m, n).float()
+    assert torch.isfinite(out).all()
+    tol = (2e-3 if not f16 else 6e-3) * max(1.0, ref.abs().max().item())
+    assert (out - ref).abs().max().item() < tol
+
+
+# fused encoder attention (attn_enc.cu) against the reference's op sequence in torch: S = Q K^T (f32), softmax(S / 8) in f32,
+# P rounded to f16, P V with f32 accumulation (wc:2183-2206).  T = 1500 is the real context; 300 / 129 / 77 are the ragged cases
+# (exp_n_audio_ctx), 2 windows x 3 heads checks the panel addressing.
+@pytest.mark.parametrize("W,H,T", [(1, 1, 128), (2, 3, 1500), (1, 2, 300), (3, 1, 129), (1, 6, 77), (1, 1, 1000)])
+def test_enc_attention_vs_torch(prod_lib, W, H, T):
+    import torch
+    torch.manual_seed(W * 1000 + H * 10 + T)
+    q = (torch.randn(W, H, T, 64, device="cuda") * 1.5).half()
+    k = (torch.randn(W, H, T, 64, device="cuda") * 1.5).half()
+    v = torch.randn(W, H, T, 64, device="cuda").half()
+    out = torch.full((W * T, H * 64), float("nan"), device="cuda", dtype=torch.float16)
+    torch.cuda.synchronize()
+    assert prod_lib.whisper_b200_test_enc_attn(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), W, H, T) == 0
+    s = q.float() @ k.float().transpose(-1, -2)
+    p = torch.softmax(s * 0.125, dim=-1).half().float()
+    ref = (p @ v.float()).permute(0, 2, 1, 3).reshape(W * T, H * 64)
+    o = out.float()
+    assert torch.isfinite(o).all()
+    err = (o - ref).abs().max().item()
+    rel = ((o - ref).norm() / ref.norm()).item()
+    assert err < 4e-3 * max(1.0, ref.abs().max().item()) and rel < 2e-3, (err, rel)
+
+
 @pytest.mark.parametrize("seconds", [0.3, 11.0, 30.0, 47.3])
 def test_mel_matches_oracle(prod_lib, ref_lib, seconds):
     pcm = synth.synth_audio(seconds, seed=7)

@@ -23,3 +23,38 @@ for n in (1, 16, 64):
 for n in (16, 64):
     for (no, k) in ((1280, 1280), (3840, 1280), (5120, 1280), (1280, 5120)):
         run("gemm_wstream", n, no, k, 48, 5)
+
+# encoder GEMM shapes at large-v3, W windows of 1500 rows (tensor roofline)
+g = lib.whisper_b200_bench_gemm
+g.restype = C.c_int
+g.argtypes = [C.c_int] * 8 + [C.POINTER(C.c_double)]
+TF_PEAK = 1400.0
+try:
+    TF_PEAK = json.load(open("MEASURED_PEAKS.json"))["bf16_tflops_sustained"]
+except Exception:
+    pass
+def gemm(name, m, n, k, f16, flags, bn=0, iters=10):
+    us = C.c_double()
+    r = g(m, n, k, f16, flags, bn, 4, iters, C.byref(us))
+    tf = 2.0 * m * n * k / (us.value * 1e-6) / 1e12 if r == 0 and us.value > 0 else 0
+    print(json.dumps({"kind": "gemm_enc", "name": name, "m": m, "n": n, "k": k, "f16": f16, "flags": flags, "bn": bn, "rc": r,
+                      "us": round(us.value, 2), "TFs": round(tf, 1), "frac_tensor": round(tf / TF_PEAK, 3)}), flush=True)
+for W in (8, 64):
+    R = W * 1500
+    for bn in (0, 256):   # 0 = persistent (auto), 256 = legacy one-tile-per-CTA kernel
+        gemm("qk", R, 2560, 1280, 1, 2 | 4, bn)
+        gemm("o_proj", R, 1280, 1280, 0, 1 | 4, bn)
+        gemm("fc1", R, 5120, 1280, 1, 4, bn)
+        gemm("fc2", R, 1280, 5120, 0, 1 | 4, bn)
+
+# fused encoder attention, large-v3: FLOPs = 4 T^2 64 H W
+fa = lib.whisper_b200_bench_enc_attn
+fa.restype = C.c_int
+fa.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+for W in (8, 64):
+    us = C.c_double()
+    r = fa(W, 20, 1500, 5, C.byref(us))
+    fl = 4.0 * 1500 * 1500 * 64 * 20 * W
+    tf = fl / (us.value * 1e-6) / 1e12 if r == 0 and us.value > 0 else 0
+    print(json.dumps({"kind": "enc_attn", "W": W, "H": 20, "T": 1500, "rc": r, "us": round(us.value, 1), "us_per_window": round(us.value / W, 1),
+                      "TFs": round(tf, 1), "frac_tensor": round(tf / TF_PEAK, 3)}), flush=True)

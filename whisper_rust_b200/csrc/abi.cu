@@ -759,7 +759,7 @@ int whisper_b200_profile_read(int category, char * name, int name_cap, double * 
     if (flops_sampled) *flops_sampled = fl[category];
     return PC_COUNT;
 }
-uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count() + step_launch_count(); }
+uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count() + step_launch_count() + enc_attn_launch_count(); }
 void whisper_b200_device_sync(struct whisper_context * ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->model.device);
@@ -776,6 +776,122 @@ int whisper_b200_test_gemm(const void * a, const void * b, void * c, int m, int 
     e.out = c; e.out_f16 = c_is_f16; e.out_mode = OUT_ROW; e.ldo = ldc; e.batch_div = 1; e.bias = bias;
     if (!gemm_f16_tc(A, B, m, n, k, 1, e, block_n, 0)) return 1;
     return cudaGetLastError() == cudaSuccess ? 0 : 2;
+    WB_CATCH(3)
+}
+// flags: 1 = accumulate into c (f32 only: c += A.B^T + bias), 2 = per-head f16 panels c[n/64][m][64]
+int whisper_b200_test_gemm_ex(const void * a, const void * b, void * c, int m, int n, int k, int lda, int ldb, int ldc, int c_is_f16,
+                              const float * bias, int block_n, int flags) {
+    WB_TRY
+    GemmOperand A{}, B{};
+    A.ptr = a; A.rows = m; A.row_stride = lda; A.batch = 1; A.phases = 1;
+    B.ptr = b; B.rows = n; B.row_stride = ldb; B.batch = 1; B.phases = 1;
+    GemmEpilogue e{};
+    e.out = c; e.out_f16 = c_is_f16; e.out_mode = (flags & 2) ? OUT_HEAD : OUT_ROW; e.ldo = ldc; e.batch_div = 1; e.bias = bias;
+    if (flags & 2) e.head_stride = (int64_t) m * 64;
+    if (flags & 1) { e.res = (const float *) c; e.ldr = ldc; }
+    if (!gemm_f16_tc(A, B, m, n, k, 1, e, block_n, 0)) return 1;
+    return cudaDeviceSynchronize() == cudaSuccess ? 0 : 2;
+    WB_CATCH(3)
+}
+
+// Encoder-GEMM micro-benchmark: C[m][n] = A[m][k] . B[n][k]^T on scratch device buffers, CUDA-event timed on the launching
+// stream; n_weights distinct B matrices are used round-robin.  flags as whisper_b200_test_gemm_ex, plus 4 = bias.
+int whisper_b200_bench_gemm(int m, int n, int k, int c_is_f16, int flags, int block_n, int n_weights, int iters, double * us_per_launch) {
+    WB_TRY
+    __half *a = nullptr, *b = nullptr;
+    void * c = nullptr;
+    float * bias = nullptr;
+    const size_t wsz = (size_t) n * k;
+    bool ok = cudaMalloc((void **) &a, (size_t) m * k * 2) == cudaSuccess && cudaMalloc((void **) &b, wsz * n_weights * 2) == cudaSuccess &&
+              cudaMalloc(&c, (size_t) m * n * 4) == cudaSuccess && cudaMalloc((void **) &bias, (size_t) n * 4) == cudaSuccess;
+    if (ok) {
+        cudaMemset(a, 0x11, (size_t) m * k * 2);
+        cudaMemset(b, 0x11, wsz * n_weights * 2);
+        cudaMemset(c, 0, (size_t) m * n * 4);
+        cudaMemset(bias, 0, (size_t) n * 4);
+    }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ok = ok && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+    auto run = [&](int i) {
+        GemmOperand A{}, B{};
+        A.ptr = a; A.rows = m; A.row_stride = k; A.batch = 1; A.phases = 1;
+        B.ptr = b + wsz * (i % n_weights); B.rows = n; B.row_stride = k; B.batch = 1; B.phases = 1;
+        GemmEpilogue e{};
+        e.out = c; e.out_f16 = c_is_f16; e.out_mode = (flags & 2) ? OUT_HEAD : OUT_ROW; e.ldo = n; e.batch_div = 1;
+        e.bias = (flags & 4) ? bias : nullptr;
+        if (flags & 2) e.head_stride = (int64_t) m * 64;
+        if (flags & 1) { e.res = (const float *) c; e.ldr = n; }
+        return gemm_f16_tc(A, B, m, n, k, 1, e, block_n, 0);
+    };
+    for (int i = 0; i < 2 && ok; ++i) ok = run(i);
+    if (ok) {
+        cudaEventRecord(e0, 0);
+        for (int i = 0; i < iters && ok; ++i) ok = run(i);
+        cudaEventRecord(e1, 0);
+        ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
+        float ms = 0.0f;
+        if (ok) cudaEventElapsedTime(&ms, e0, e1);
+        if (us_per_launch) *us_per_launch = 1e3 * ms / std::max(1, iters);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(bias);
+    return ok ? 0 : 1;
+    WB_CATCH(3)
+}
+// fused encoder attention on device buffers: q, k, v f16 [W][H][T][64] (plain layout; repacked here into the kernel's panels)
+int whisper_b200_test_enc_attn(const void * q, const void * k, const void * v, void * out, int W, int H, int T) {
+    WB_TRY
+    const int R = W * T, Tpad = (int) pad_to(T, 8), S = H * 64;
+    __half *qk = nullptr, *vT = nullptr;
+    if (cudaMalloc((void **) &qk, (size_t) 2 * H * R * 64 * 2) != cudaSuccess) return 1;
+    if (cudaMalloc((void **) &vT, (size_t) H * W * 64 * Tpad * 2) != cudaSuccess) { cudaFree(qk); return 1; }
+    cudaMemset(vT, 0, (size_t) H * W * 64 * Tpad * 2);
+    std::vector<__half> hq((size_t) W * H * T * 64), hk(hq.size()), hv(hq.size()), pqk((size_t) 2 * H * R * 64), pv((size_t) H * W * 64 * Tpad);
+    cudaMemcpy(hq.data(), q, hq.size() * 2, cudaMemcpyDeviceToHost);
+    cudaMemcpy(hk.data(), k, hk.size() * 2, cudaMemcpyDeviceToHost);
+    cudaMemcpy(hv.data(), v, hv.size() * 2, cudaMemcpyDeviceToHost);
+    memset(pv.data(), 0, pv.size() * 2);
+    for (int w = 0; w < W; ++w)
+        for (int h = 0; h < H; ++h)
+            for (int t = 0; t < T; ++t)
+                for (int d = 0; d < 64; ++d) {
+                    const size_t src = (((size_t) w * H + h) * T + t) * 64 + d;
+                    pqk[((size_t) h * R + (size_t) w * T + t) * 64 + d] = hq[src];
+                    pqk[((size_t) (H + h) * R + (size_t) w * T + t) * 64 + d] = hk[src];
+                    pv[(((size_t) h * W + w) * 64 + d) * Tpad + t] = hv[src];
+                }
+    cudaMemcpy(qk, pqk.data(), pqk.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(vT, pv.data(), pv.size() * 2, cudaMemcpyHostToDevice);
+    const bool ok = enc_attention(qk, vT, (__half *) out, W, T, Tpad, H, S, 0.125f, 0) && cudaDeviceSynchronize() == cudaSuccess;
+    cudaFree(qk); cudaFree(vT);
+    return ok ? 0 : 2;
+    WB_CATCH(3)
+}
+// micro-benchmark of the fused encoder attention: W windows x H heads x T frames; returns microseconds per launch
+int whisper_b200_bench_enc_attn(int W, int H, int T, int iters, double * us_per_launch) {
+    WB_TRY
+    const int R = W * T, Tpad = (int) pad_to(T, 8), S = H * 64;
+    __half *qk = nullptr, *vT = nullptr, *out = nullptr;
+    bool ok = cudaMalloc((void **) &qk, (size_t) 2 * H * R * 64 * 2) == cudaSuccess && cudaMalloc((void **) &vT, (size_t) H * W * 64 * Tpad * 2) == cudaSuccess &&
+              cudaMalloc((void **) &out, (size_t) R * S * 2) == cudaSuccess;
+    if (ok) { cudaMemset(qk, 0x11, (size_t) 2 * H * R * 64 * 2); cudaMemset(vT, 0x11, (size_t) H * W * 64 * Tpad * 2); }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ok = ok && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+    for (int i = 0; i < 2 && ok; ++i) ok = enc_attention(qk, vT, out, W, T, Tpad, H, S, 0.125f, 0);
+    if (ok) {
+        cudaEventRecord(e0, 0);
+        for (int i = 0; i < iters && ok; ++i) ok = enc_attention(qk, vT, out, W, T, Tpad, H, S, 0.125f, 0);
+        cudaEventRecord(e1, 0);
+        ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
+        float ms = 0.0f;
+        if (ok) cudaEventElapsedTime(&ms, e0, e1);
+        if (us_per_launch) *us_per_launch = 1e3 * ms / std::max(1, iters);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(qk); cudaFree(vT); cudaFree(out);
+    return ok ? 0 : 1;
     WB_CATCH(3)
 }
 int whisper_b200_test_mel(struct whisper_context * ctx, const float * d_pcm, int n_samples, float * d_mel) {

@@ -100,6 +100,12 @@ __device__ __forceinline__ void tma_load_4d(void * dst, const CUtensorMap * m, u
         "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_2d(void * dst, const CUtensorMap * m, uint64_t * bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(
+                     smem_u32(dst)),
+                 "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+                 : "memory");
+}
 // 1-D bulk copy global -> shared (bytes multiple of 16, both 16-byte aligned)
 __device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint32_t bytes, uint64_t * bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(smem_u32(dst)),
@@ -133,6 +139,22 @@ __device__ __forceinline__ void bulk_load_1d_hint(void * dst, const void * src, 
                  "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
                  : "memory");
 }
+// TMA stores (shared -> global through a tensor map), bulk-group completion
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap * m, const void * src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n" ::"l"(m), "r"(smem_u32(src)),
+                 "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+// element-wise add into global memory, performed at the L2 (f32 per the tensor map's data type)
+__device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap * m, const void * src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n" ::"l"(m),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+// at most N committed bulk groups still READING their shared-memory source
+template <int N> __device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_group() { asm volatile("cp.async.bulk.wait_group %0;\n" ::"n"(N) : "memory"); }
 // named barrier over a subset of the CTA's warps (id 1..15; id 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(int id, int n_threads) { asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(n_threads) : "memory"); }
 // programmatic dependent launch (PDL): let the next kernel of the stream start its prologue / wait for the previous one

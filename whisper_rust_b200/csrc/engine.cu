@@ -284,6 +284,16 @@ State * state_create(Context * ctx) {
 // =============================================================================================
 // workspaces
 // =============================================================================================
+// WB200_ATTN=legacy: materialised scores + softmax kernel + P.V GEMM (the round-1 v2 path; kept for A/B measurements)
+static bool legacy_attention() {
+    static int v = -1;
+    if (v < 0) {
+        const char * e = getenv("WB200_ATTN");
+        v = (e && strcmp(e, "legacy") == 0) ? 1 : 0;
+    }
+    return v == 1;
+}
+
 static bool ensure_enc_ws(Context & ctx, int windows, int T) {
     EncWorkspace & ws = ctx.enc_ws;
     if (ws.base && ws.windows >= windows && ws.T == T) return true;
@@ -302,8 +312,9 @@ static bool ensure_enc_ws(Context & ctx, int windows, int T) {
     const size_t R = (size_t) W * T;
     const size_t o_melT = take((size_t) W * (2 * T + 2) * m.kc1 * 2), o_h1 = take((size_t) W * (2 * T + 2) * S * 2);
     const size_t o_x = take(R * S * 4), o_xa = take(R * S * 2), o_qk = take(2 * R * S * 2);
-    const size_t o_vT = take((size_t) H * W * 64 * Tpad * 2), o_sc = take((size_t) H * W * T * Tpad * 4);
-    const size_t o_p = take((size_t) H * W * T * Tpad * 2), o_att = take(R * S * 2), o_hb = take(R * 4 * S * 2);
+    const bool legacy = legacy_attention();
+    const size_t o_vT = take((size_t) H * W * 64 * Tpad * 2), o_sc = take(legacy ? (size_t) H * W * T * Tpad * 4 : 16);
+    const size_t o_p = take(legacy ? (size_t) H * W * T * Tpad * 2 : 16), o_att = take(R * S * 2), o_hb = take(R * 4 * S * 2);
     const size_t o_e16 = take(R * S * 2), o_e32 = take(R * S * 4);
     WB_CUDA_OK(cudaMalloc((void **) &ws.base, off));
     WB_CUDA_OK(cudaMemset(ws.base, 0, off));  // conv padding rows and the V^T / P tails must start as zeros
@@ -487,6 +498,10 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
             e.bias = l.v.b;
             if (!gemm_f16_tc(opnd(ws.xa, R, S), opnd(l.v.w, S, S), R, S, S, 1, e, 0, s)) return false;
         }
+        if (!legacy_attention()) {
+            // fused: softmax(Q K^T * D^-1/2) V with the scores in TMEM (wc:2183-2206)
+            if (!enc_attention(ws.qk, ws.vT, ws.att, W, T, Tpad, H, S, kq_scale, s)) return false;
+        } else {
         {   // scores = Q K^T per (head, window)  (wc:2189)
             GemmEpilogue e = epi_row(ws.sc, false, Tpad);
             e.out_batch_stride = (int64_t) T * Tpad;
@@ -504,6 +519,7 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
                              opnd(ws.vT, 64, Tpad, (int64_t) H * W, (int64_t) 64 * Tpad), T, 64, T, H * W, e, 64, s))
                 return false;
         }
+        }
         {   // output projection + bias + residual (wc:2212-2220)
             GemmEpilogue e = epi_row(ws.x, false, S);
             e.bias = l.o.b; e.res = ws.x; e.ldr = S;
@@ -511,9 +527,12 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
         }
         if (!layernorm_rows(ws.x, R, S, l.ln2.g, l.ln2.b, hp.eps, ws.xa, nullptr, s)) return false;
         {   // MLP (wc:2237-2254)
+            // fc1 stores h = f16(W1.x + b1), the index of the reference's GELU table lookup; the lookup itself is a separate
+            // shared-memory-table pass (a gather from the 128 KB table inside the GEMM epilogue costs more than the GEMM)
             GemmEpilogue e = epi_row(ws.hb, true, 4 * S);
-            e.bias = l.fc1.b; e.gelu_table = m.gelu_table;
+            e.bias = l.fc1.b;
             if (!gemm_f16_tc(opnd(ws.xa, R, S), opnd(l.fc1.w, 4 * S, S), R, 4 * S, S, 1, e, 0, s)) return false;
+            if (!gelu_table_inplace(ws.hb, (int64_t) R * 4 * S, m.gelu_table, s)) return false;
             GemmEpilogue e2 = epi_row(ws.x, false, S);
             e2.bias = l.fc2.b; e2.res = ws.x; e2.ldr = S;
             if (!gemm_f16_tc(opnd(ws.hb, R, 4 * S), opnd(l.fc2.w, S, 4 * S), R, S, 4 * S, 1, e2, 0, s)) return false;
@@ -541,7 +560,9 @@ bool stage_encode(Context & ctx, State * const * states, const int * mel_offsets
     WB_CUDA_OK(cudaSetDevice(ctx.model.device));
     const int64_t t0 = time_us();
     const auto & hp = ctx.model.hp;
-    static const int kMaxWindows = 8;  // encoder rows per batch = 8 x 1500; bounds the attention-score workspace
+    // windows per encoder pass: the legacy attention path materialises [H][W][T][T] scores; the fused path only needs
+    // activations (64 windows of large-v3: ~2.6 GB), and more rows per GEMM means fuller waves on the 148 SMs
+    const int kMaxWindows = legacy_attention() ? 8 : 64;
     int i = 0;
     while (i < n_states) {
         const int T = states[i]->exp_n_audio_ctx > 0 ? states[i]->exp_n_audio_ctx : hp.n_audio_ctx;

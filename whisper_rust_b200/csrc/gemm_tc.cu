@@ -14,7 +14,10 @@
 #include "gemm_tc.cuh"
 #include "prof.h"
 
+#include <algorithm>
 #include <atomic>
+#include <cstdlib>
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -245,6 +248,227 @@ gemm_f16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Persistent variant for the large encoder GEMMs (one CTA per SM, static round-robin tile scheduler).
+//   * TMEM holds TWO accumulators (2 x BLOCK_N columns): the MMA warp starts tile i+1 while the epilogue
+//     warps drain tile i  (tmem_full / tmem_empty mbarriers).
+//   * The epilogue never touches global memory through the LSU: each warp transposes its 32-row slab
+//     chunk by chunk through a 128-byte-swizzled shared-memory buffer and hands it to TMA
+//     (cp.async.bulk.tensor store).  The residual GEMMs (x += W.y + b: wc:2216-2220, 2251-2254) use
+//     cp.reduce.async.bulk.tensor .add: the f32 addition is done at the L2, x is never loaded by the SM.
+//     fl(x + (acc + b)) == fl((acc + b) + x): same rounding as the reference's ggml_add.
+// ---------------------------------------------------------------------------------------------
+struct PersistEpi {
+    const float * bias;
+    int64_t       bias_batch_stride;
+    float         scale;
+    int           scale_n0, scale_n1;
+    int           head_mode;   // 0: coords (n, m, 0, b)   1: per-head panels, coords (0, m, n / 64, b)
+    int           accumulate;  // f32 only: out += value
+};
+
+__host__ __device__ constexpr int pgemm_stages(int block_n) { return block_n >= 256 ? 4 : 6; }
+static constexpr int kEpiBufBytes = 32 * 128;               // 32 rows x 128 B (32 f32 or 64 f16 columns)
+static constexpr int kEpiBytes    = 4 * 2 * kEpiBufBytes;   // 4 warps x 2 buffers
+__host__ __device__ constexpr int pgemm_smem_bytes(int block_n) {
+    return pgemm_stages(block_n) * gemm_stage_bytes(block_n) + kEpiBytes + 1024 + 256;
+}
+
+template <int BLOCK_N, bool kF16>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_f16_persist_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                        const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, int batch, int a_bcast, int b_bcast,
+                        PersistEpi epi) {
+    constexpr int kStages     = pgemm_stages(BLOCK_N);
+    constexpr int kStageBytes = gemm_stage_bytes(BLOCK_N);
+    constexpr int kABytes     = BLOCK_M * BLOCK_K * 2;
+    constexpr int kChunkCols  = kF16 ? 64 : 32;  // columns per 128-byte staging row
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    uint8_t * epi_smem = smem + kStages * kStageBytes;
+
+    uint64_t * full_bar   = (uint64_t *) (epi_smem + kEpiBytes);
+    uint64_t * empty_bar  = full_bar + kStages;
+    uint64_t * tmem_full  = empty_bar + kStages;
+    uint64_t * tmem_empty = tmem_full + 2;
+    uint32_t * tmem_slot  = (uint32_t *) (tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    const int n_tiles = (N + BLOCK_N - 1) / BLOCK_N;
+    const int total   = m_tiles * n_tiles * batch;
+    const int num_kb  = (K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        tma_prefetch_desc(&tmap_c);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar + s, 1);
+            mbar_init(empty_bar + s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tmem_full + a, 1);
+            mbar_init(tmem_empty + a, 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int n0 = (t % n_tiles) * BLOCK_N;
+                const int m0 = ((t / n_tiles) % m_tiles) * BLOCK_M;
+                const int b  = t / (n_tiles * m_tiles);
+                const int ba = a_bcast ? 0 : b, bb = b_bcast ? 0 : b;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty_bar + stage, phase ^ 1);
+                    uint8_t * sa = smem + stage * kStageBytes;
+                    mbar_expect_tx(full_bar + stage, kStageBytes);
+                    tma_load_4d(sa, &tmap_a, full_bar + stage, kb * BLOCK_K, 0, m0, ba);
+                    tma_load_4d(sa + kABytes, &tmap_b, full_bar + stage, kb * BLOCK_K, 0, n0, bb);
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_f16(BLOCK_M, BLOCK_N);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);  // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t) (acc * BLOCK_N);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full_bar + stage, phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    const uint64_t da = umma_desc_k_sw128(sa);
+                    const uint64_t db = umma_desc_k_sw128(sa + kABytes);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / 16; ++k) {
+                        umma_f16_ss(d_tmem, da + (uint64_t) (2 * k), db + (uint64_t) (2 * k), idesc, (kb | k) != 0);
+                    }
+                    umma_commit(empty_bar + stage);
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(tmem_full + acc);
+                if ((acc ^= 1) == 0) acc_phase ^= 1;
+            }
+        }
+    } else {
+        // ---------------- epilogue warps 2..5: TMEM lane quadrant = warp % 4 ----------------
+        const int grp = warp & 3;
+        uint8_t * my_buf = epi_smem + grp * 2 * kEpiBufBytes;
+        const uint32_t row_off = (uint32_t) lane * 128u;
+        const uint32_t sw = (uint32_t) (lane & 7);
+        int acc = 0, buf = 0;
+        uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int n0 = (t % n_tiles) * BLOCK_N;
+            const int m0 = ((t / n_tiles) % m_tiles) * BLOCK_M;
+            const int b  = t / (n_tiles * m_tiles);
+            const int mw = m0 + grp * 32;  // first row of this warp's slab
+            const float * bias = epi.bias ? epi.bias + (int64_t) b * epi.bias_batch_stride : nullptr;
+
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            if (mw < M) {
+                const uint32_t t_acc = tmem_base + ((uint32_t) (grp * 32) << 16) + (uint32_t) (acc * BLOCK_N);
+#pragma unroll 1
+                for (int c = 0; c < BLOCK_N / kChunkCols; ++c) {
+                    const int nc = n0 + c * kChunkCols;
+                    if (nc >= N) break;
+                    uint32_t r[kChunkCols];
+                    {
+                        uint32_t (&r0)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[0]);
+                        tmem_ld_32x32(t_acc + (uint32_t) (c * kChunkCols), r0);
+                        if constexpr (kF16) {
+                            uint32_t (&r1)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[32]);
+                            tmem_ld_32x32(t_acc + (uint32_t) (c * kChunkCols + 32), r1);
+                        }
+                    }
+                    // bias values of this chunk: lane j holds column nc + j (and nc + 32 + j)
+                    float bv0 = 0.0f, bv1 = 0.0f;
+                    if (bias != nullptr) {
+                        if (nc + lane < N) bv0 = __ldg(bias + nc + lane);
+                        if (kF16 && nc + 32 + lane < N) bv1 = __ldg(bias + nc + 32 + lane);
+                    }
+                    tmem_ld_wait();
+                    float v[kChunkCols];
+#pragma unroll
+                    for (int j = 0; j < kChunkCols; ++j) {
+                        float x = __uint_as_float(r[j]);
+                        if (bias != nullptr) x = __fadd_rn(x, __shfl_sync(0xffffffffu, j < 32 ? bv0 : bv1, j & 31));
+                        const int n = nc + j;
+                        if (n >= epi.scale_n0 && n < epi.scale_n1) x = __fmul_rn(x, epi.scale);
+                        v[j] = x;
+                    }
+                    // the TMA store issued two chunks ago from this buffer must have finished reading it
+                    if (lane == 0) bulk_wait_group_read<1>();
+                    __syncwarp();
+                    uint8_t * dst = my_buf + buf * kEpiBufBytes + row_off;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        uint4 pk;
+                        if constexpr (kF16) {
+                            __half2 h0 = __floats2half2_rn(v[q * 8 + 0], v[q * 8 + 1]);
+                            __half2 h1 = __floats2half2_rn(v[q * 8 + 2], v[q * 8 + 3]);
+                            __half2 h2 = __floats2half2_rn(v[q * 8 + 4], v[q * 8 + 5]);
+                            __half2 h3 = __floats2half2_rn(v[q * 8 + 6], v[q * 8 + 7]);
+                            pk.x = *(uint32_t *) &h0; pk.y = *(uint32_t *) &h1; pk.z = *(uint32_t *) &h2; pk.w = *(uint32_t *) &h3;
+                        } else {
+                            pk.x = __float_as_uint(v[q * 4 + 0]); pk.y = __float_as_uint(v[q * 4 + 1]);
+                            pk.z = __float_as_uint(v[q * 4 + 2]); pk.w = __float_as_uint(v[q * 4 + 3]);
+                        }
+                        *(uint4 *) (dst + (((uint32_t) q ^ sw) << 4)) = pk;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        const void * src = my_buf + buf * kEpiBufBytes;
+                        const int c0 = epi.head_mode ? 0 : nc, c2 = epi.head_mode ? (nc >> 6) : 0;
+                        if (epi.accumulate) tma_reduce_add_4d(&tmap_c, src, c0, mw, c2, b);
+                        else tma_store_4d(&tmap_c, src, c0, mw, c2, b);
+                        bulk_commit_group();
+                    }
+                    buf ^= 1;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + acc);
+            if ((acc ^= 1) == 0) acc_phase ^= 1;
+        }
+        if (lane == 0) bulk_wait_group<0>();
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<2 * BLOCK_N>(tmem_base);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side: tensor-map construction (driver entry point fetched through the runtime) and launch
 // ---------------------------------------------------------------------------------------------
@@ -335,6 +559,98 @@ static bool launch_gemm(const CUtensorMap & ta, const CUtensorMap & tb, int M, i
     return true;
 }
 
+
+// ---- persistent path: output tensor map + launch -------------------------------------------------
+static int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+static int gemm_mode_env() {  // WB200_GEMM=legacy forces the one-tile-per-CTA kernel (A/B measurements)
+    static int mode = -1;
+    if (mode < 0) {
+        const char * e = getenv("WB200_GEMM");
+        mode = (e && strcmp(e, "legacy") == 0) ? 1 : 0;
+    }
+    return mode;
+}
+
+// 4-D view of the output for TMA stores: row mode {N, M, 1, batch}; head mode {64, M, N/64, batch}; box = 32 rows x 128 bytes
+static bool make_tmap_out(CUtensorMap * out, const GemmEpilogue & e, int M, int N, int batch) {
+    PFN_encodeTiled enc = get_encode_fn();
+    WB_CHECK(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable\n");
+    const int es = e.out_f16 ? 2 : 4;
+    const bool head = e.out_mode == OUT_HEAD;
+    const int64_t bstride = (batch > 1 || e.out_batch_stride > 0) && e.out_batch_stride > 0 ? e.out_batch_stride
+                                                                                             : (head ? (int64_t) (N / 64) * e.head_stride : (int64_t) M * e.ldo);
+    cuuint64_t dims[4];
+    cuuint64_t strides[3];
+    if (head) {
+        dims[0] = 64; dims[1] = (cuuint64_t) M; dims[2] = (cuuint64_t) (N / 64); dims[3] = (cuuint64_t) batch;
+        strides[0] = 64 * es; strides[1] = (cuuint64_t) e.head_stride * es; strides[2] = (cuuint64_t) bstride * es;
+    } else {
+        dims[0] = (cuuint64_t) N; dims[1] = (cuuint64_t) M; dims[2] = 1; dims[3] = (cuuint64_t) batch;
+        strides[0] = (cuuint64_t) e.ldo * es; strides[1] = (cuuint64_t) e.ldo * es * (cuuint64_t) M; strides[2] = (cuuint64_t) bstride * es;
+    }
+    cuuint32_t box[4]  = {(cuuint32_t) (128 / es), 32, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(out, e.out_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e.out, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    WB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(out) failed: %d (M=%d N=%d batch=%d ldo=%lld head=%d)\n", (int) r, M, N, batch,
+             (long long) e.ldo, (int) head);
+    return true;
+}
+
+// can this GEMM run on the persistent kernel?
+static bool persist_eligible(const GemmEpilogue & e, const GemmTaps & taps, int M, int N, int batch) {
+    if (gemm_mode_env() == 1) return false;
+    if (taps.taps != 1 || e.gelu_table != nullptr || e.batch_div != 1 || e.rows_per_panel != 0) return false;
+    if (e.out_mode != OUT_ROW && e.out_mode != OUT_HEAD) return false;
+    const int es = e.out_f16 ? 2 : 4;
+    if (((uintptr_t) e.out & 15) != 0) return false;
+    if (e.out_mode == OUT_ROW && (((e.ldo * es) & 15) != 0 || e.ldo < N)) return false;
+    if (e.out_mode == OUT_HEAD && (!e.out_f16 || (N & 63) != 0 || ((e.head_stride * es) & 15) != 0)) return false;
+    if (batch > 1 && ((e.out_batch_stride * es) & 15) != 0) return false;
+    if (e.res != nullptr) {  // only the in-place residual  out += ...
+        if (e.res != (const float *) e.out || e.out_f16 || e.out_mode != OUT_ROW || e.ldr != e.ldo || e.res_row_mod != 0) return false;
+        if (batch > 1 && e.res_batch_stride != e.out_batch_stride) return false;
+    }
+    // worth it only when there are at least as many 128 x 128 tiles as SMs
+    return (int64_t) ceil_div(M, BLOCK_M) * ceil_div(N, 128) * batch >= sm_count();
+}
+
+template <int BN, bool F16>
+static bool launch_gemm_persist(const CUtensorMap & ta, const CUtensorMap & tb, const CUtensorMap & tc, int M, int N, int K, int batch,
+                                int a_bcast, int b_bcast, const GemmEpilogue & e, cudaStream_t stream) {
+    static bool attr_set = false;
+    constexpr int smem = pgemm_smem_bytes(BN);
+    if (!attr_set) {
+        WB_CUDA_OK(cudaFuncSetAttribute(gemm_f16_persist_kernel<BN, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    PersistEpi pe{};
+    pe.bias = e.bias; pe.bias_batch_stride = e.bias_batch_stride;
+    pe.scale = e.scale; pe.scale_n0 = e.scale_n0; pe.scale_n1 = e.scale_n1;
+    pe.head_mode = e.out_mode == OUT_HEAD ? 1 : 0;
+    pe.accumulate = e.res != nullptr ? 1 : 0;
+    const int64_t tiles = (int64_t) ceil_div(M, BLOCK_M) * ceil_div(N, BN) * batch;
+    const int grid = (int) std::min<int64_t>(tiles, sm_count());
+    ProfScope prof_scope(g_prof_gemm_cat, stream,
+                         (double) batch * ((double) M * K * 2 * (a_bcast ? 1.0 / batch : 1.0) + (double) N * K * 2 * (b_bcast ? 1.0 / batch : 1.0) +
+                                          (double) M * N * (e.out_f16 ? 2 : 4)),
+                         2.0 * batch * M * N * (double) K);
+    gemm_f16_persist_kernel<BN, F16><<<grid, GEMM_THREADS, smem, stream>>>(ta, tb, tc, M, N, K, batch, a_bcast, b_bcast, pe);
+    WB_CUDA_OK(cudaGetLastError());
+    g_gemm_launches.fetch_add(1);
+    return true;
+}
+
 bool gemm_f16_tc(const GemmOperand & A, const GemmOperand & B, int M, int N, int K, int batch, const GemmEpilogue & epi_in, int block_n,
                  cudaStream_t stream, const GemmTaps * taps_in) {
     GemmEpilogue epi = epi_in;
@@ -346,6 +662,19 @@ bool gemm_f16_tc(const GemmOperand & A, const GemmOperand & B, int M, int N, int
     const int b_bcast = (B.batch <= 1 && batch > 1) ? 1 : 0;
     const int Kb = taps.taps * (taps.taps > 1 ? taps.k_tap : K);  // extent of B's k dimension
     WB_CHECK(M > 0 && N > 0 && K > 0 && batch > 0, "bad GEMM shape %d %d %d %d\n", M, N, K, batch);
+    if (block_n == 0 && persist_eligible(epi, taps, M, N, batch)) {
+        const int bn = ((int64_t) ceil_div(M, BLOCK_M) * ceil_div(N, 256) * batch >= 2 * sm_count() || N % 256 == 0) ? 256 : 128;
+        CUtensorMap ta, tb, tc;
+        if (!make_tmap(&ta, A, K, BLOCK_M)) return false;
+        if (!make_tmap(&tb, B, K, bn)) return false;
+        if (!make_tmap_out(&tc, epi, M, N, batch)) return false;
+        if (bn == 256) {
+            return epi.out_f16 ? launch_gemm_persist<256, true>(ta, tb, tc, M, N, K, batch, a_bcast, b_bcast, epi, stream)
+                               : launch_gemm_persist<256, false>(ta, tb, tc, M, N, K, batch, a_bcast, b_bcast, epi, stream);
+        }
+        return epi.out_f16 ? launch_gemm_persist<128, true>(ta, tb, tc, M, N, K, batch, a_bcast, b_bcast, epi, stream)
+                           : launch_gemm_persist<128, false>(ta, tb, tc, M, N, K, batch, a_bcast, b_bcast, epi, stream);
+    }
     if (block_n == 0) {
         // enough CTAs to cover the 148 SMs for weight streaming at small M; wide tiles for big M
         const int64_t mt = ceil_div(M, BLOCK_M) * (int64_t) batch;

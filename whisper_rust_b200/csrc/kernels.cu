@@ -6,6 +6,7 @@
 #include "kernels.cuh"
 #include "prof.h"
 
+#include <algorithm>
 #include <atomic>
 #include <math.h>
 
@@ -308,6 +309,52 @@ bool softmax_rows_f16(const float * s, int64_t rows, int n, int64_t lds, float s
     ProfScope prof_scope(PC_ENC_SOFTMAX, stream, (double) rows * n * 6);
     if (rows <= 0) return true;
     softmax_rows_kernel<<<(unsigned) ceil_div64(rows, 8), 256, 0, stream>>>(s, rows, n, lds, scale, p, ldp);
+    WB_LAUNCHED();
+    return true;
+}
+
+// =============================================================================================
+// GELU through the reference's 65,536-entry f16 table (ggml-cpu/vec.h:571-585), in place on an f16 tensor.
+// The fc1 GEMM stores h = f16(W1.x + b1) - the value the reference's lookup is indexed by - and this pass maps h -> table[h].
+// The table sits in shared memory (128 KB): a warp's 32 random lookups cost ~3-4 bank cycles instead of up to 32 L1 wavefronts.
+// =============================================================================================
+__global__ void __launch_bounds__(512, 1)
+gelu_table_kernel(__half * __restrict__ x, int64_t n8 /* groups of 8 halves */, const __half * __restrict__ table) {
+    extern __shared__ uint4 gelu_tab_raw[];
+    uint16_t * tab = (uint16_t *) gelu_tab_raw;
+    const uint4 * tsrc = (const uint4 *) table;
+    for (int i = threadIdx.x; i < 65536 * 2 / 16; i += blockDim.x) gelu_tab_raw[i] = __ldg(tsrc + i);
+    __syncthreads();
+    uint4 * xv = (uint4 *) x;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t) gridDim.x * blockDim.x) {
+        uint4 v = xv[i];
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t lo = w[k] & 0xffffu, hi = w[k] >> 16;
+            // x <= -10 -> 0, x >= 10 -> x (vec.h:575-580); f16 bit patterns: 10.0 = 0x4900, -10.0 = 0xC900
+            const uint32_t alo = lo & 0x7fffu, ahi = hi & 0x7fffu;
+            uint32_t rlo = tab[lo], rhi = tab[hi];
+            if (alo >= 0x4900u && alo <= 0x7c00u) rlo = (lo & 0x8000u) ? 0u : lo;
+            if (ahi >= 0x4900u && ahi <= 0x7c00u) rhi = (hi & 0x8000u) ? 0u : hi;
+            w[k] = rlo | (rhi << 16);
+        }
+        xv[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        WB_CUDA_OK(cudaFuncSetAttribute(gelu_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536 * 2));
+        attr_set = true;
+    }
+    WB_CHECK(n % 8 == 0 && ((uintptr_t) x & 15) == 0, "gelu_table_inplace: %lld elements must be a multiple of 8, 16-byte aligned\n", (long long) n);
+    ProfScope prof_scope(PC_OTHER, stream, (double) n * 4);
+    const int64_t n8 = n / 8;
+    const int grid = (int) std::min<int64_t>(ceil_div64(n8, 512), 148 * 2);
+    if (grid <= 0) return true;
+    gelu_table_kernel<<<grid, 512, 65536 * 2, stream>>>(x, n8, table);
     WB_LAUNCHED();
     return true;
 }

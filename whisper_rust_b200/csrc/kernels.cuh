@@ -36,6 +36,15 @@ bool layernorm_rows(const float * x, int rows, int S, const float * gamma, const
 // row softmax with scale (ggml_soft_max_ext, ops.cpp:4731-4827): p = softmax(s*scale) -> f16
 bool softmax_rows_f16(const float * s, int64_t rows, int n, int64_t lds, float scale, __half * p, int64_t ldp, cudaStream_t stream);
 
+// in place x[i] = gelu_table[x[i]] with the reference's clamps (x <= -10 -> 0, x >= 10 -> x): ggml-cpu/vec.h:571-585
+bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_t stream);
+
+// fused encoder self-attention (attn_enc.cu): qk f16 per-head panels [2H][R][64] (Q heads then K heads, R = W*T), vT f16
+// [H][W][64][Tpad], out f16 [R][S]; softmax(Q K^T * scale) V   (whisper.cpp:2183-2206)
+bool enc_attention(const __half * qk, const __half * vT, __half * out, int W, int T, int Tpad, int H, int S, float scale,
+                   cudaStream_t stream);
+uint64_t enc_attn_launch_count();
+
 // ------------------------------------------------------------------------------------------
 // decoder step kernels
 // ------------------------------------------------------------------------------------------
