@@ -241,9 +241,22 @@ def main():
             ms = float(t.item())
         return ms, launches, d2h // max(1, args.steps)
 
+    def counters():
+        """per-state host-clock phase counters of the library (wc:868-881 equivalents), summed over the batch: microseconds"""
+        tot = np.zeros(6, dtype=np.int64)
+        for st in states:
+            c7, us6 = (C.c_int32 * 7)(), (C.c_int64 * 6)()
+            lib.whisper_b200_get_counters(st.ptr, c7, us6)
+            tot += np.array(list(us6), dtype=np.int64)
+        return tot
+
     lib.whisper_b200_profile(20000)
+    c0 = counters()
     with ClockSampler(local_rank) as clk:
         ms_dev, launches, _ = timed(dev_sets, False)
+    c1 = counters()
+    phase = {k: round(float(c1[i] - c0[i]) / 1e3 / args.steps, 2) for i, k in
+             enumerate(("sample", "encode", "decode_step", "decode_batch", "prompt", "mel"))}
     cats = {}
     ncat = lib.whisper_b200_profile_read(0, None, 0, None, None, None, None, None)
     for c in range(ncat):
@@ -298,6 +311,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
             "roofline": roofline,
+            "phase_ms_per_step_host_clock": phase,
             "kernel_breakdown_ms_per_step_est": {k: round(x / args.steps, 3) for k, x in sorted(est.items(), key=lambda kv: -kv[1])},
         }
         if world == 1 and not args.no_cpu_baseline and cf.ORACLE_LIB.exists():

@@ -59,9 +59,10 @@ WHISPER_API int whisper_b200_test_gemm_ex(const void * a_f16, const void * b_f16
 WHISPER_API int whisper_b200_bench_gemm(int m, int n, int k, int c_is_f16, int flags, int block_n, int n_weights, int iters,
                                         double * us_per_launch);
 /* fused encoder self-attention softmax(Q K^T / 8) V on device buffers: q, k, v f16 [W][H][T][64], out f16 [W*T][H*64] */
+/* v_transposed: 0 = V in [t][64] panels like Q and K (MN-major MMA operand), 1 = V^T panels [64][t] */
 WHISPER_API int whisper_b200_test_enc_attn(const void * q_f16, const void * k_f16, const void * v_f16, void * out_f16, int n_windows, int n_head,
-                                           int n_ctx);
-WHISPER_API int whisper_b200_bench_enc_attn(int n_windows, int n_head, int n_ctx, int iters, double * us_per_launch);
+                                           int n_ctx, int v_transposed);
+WHISPER_API int whisper_b200_bench_enc_attn(int n_windows, int n_head, int n_ctx, int iters, int v_transposed, double * us_per_launch);
 /* log-mel of device PCM -> device mel [n_mel][n_len] using the context's filterbank */
 WHISPER_API int whisper_b200_test_mel(struct whisper_context * ctx, const float * d_pcm, int n_samples, float * d_mel);
 /* the decode-step cross-attention kernel on device buffers: q f16 [n][S], kv f16 [2H][T][64] per row (same kv for all rows) */

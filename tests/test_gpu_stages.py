@@ -73,8 +73,9 @@ def test_gemm_persistent_vs_torch(prod_lib, m, n, k, f16, flags):
 # fused encoder attention (attn_enc.cu) against the reference's op sequence in torch: S = Q K^T (f32), softmax(S / 8) in f32,
 # P rounded to f16, P V with f32 accumulation (wc:2183-2206).  T = 1500 is the real context; 300 / 129 / 77 are the ragged cases
 # (exp_n_audio_ctx), 2 windows x 3 heads checks the panel addressing.
+@pytest.mark.parametrize("vt", [0, 1])
 @pytest.mark.parametrize("W,H,T", [(1, 1, 128), (2, 3, 1500), (1, 2, 300), (3, 1, 129), (1, 6, 77), (1, 1, 1000)])
-def test_enc_attention_vs_torch(prod_lib, W, H, T):
+def test_enc_attention_vs_torch(prod_lib, W, H, T, vt):
     import torch
     torch.manual_seed(W * 1000 + H * 10 + T)
     q = (torch.randn(W, H, T, 64, device="cuda") * 1.5).half()
@@ -82,7 +83,7 @@ def test_enc_attention_vs_torch(prod_lib, W, H, T):
     v = torch.randn(W, H, T, 64, device="cuda").half()
     out = torch.full((W * T, H * 64), float("nan"), device="cuda", dtype=torch.float16)
     torch.cuda.synchronize()
-    assert prod_lib.whisper_b200_test_enc_attn(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), W, H, T) == 0
+    assert prod_lib.whisper_b200_test_enc_attn(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), W, H, T, vt) == 0
     s = q.float() @ k.float().transpose(-1, -2)
     p = torch.softmax(s * 0.125, dim=-1).half().float()
     ref = (p @ v.float()).permute(0, 2, 1, 3).reshape(W * T, H * 64)

@@ -50,11 +50,11 @@ for W in (8, 64):
 # fused encoder attention, large-v3: FLOPs = 4 T^2 64 H W
 fa = lib.whisper_b200_bench_enc_attn
 fa.restype = C.c_int
-fa.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
-for W in (8, 64):
+fa.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+for W, vt in ((8, 0), (64, 0), (64, 1)):
     us = C.c_double()
-    r = fa(W, 20, 1500, 5, C.byref(us))
+    r = fa(W, 20, 1500, 5, vt, C.byref(us))
     fl = 4.0 * 1500 * 1500 * 64 * 20 * W
     tf = fl / (us.value * 1e-6) / 1e12 if r == 0 and us.value > 0 else 0
-    print(json.dumps({"kind": "enc_attn", "W": W, "H": 20, "T": 1500, "rc": r, "us": round(us.value, 1), "us_per_window": round(us.value / W, 1),
+    print(json.dumps({"kind": "enc_attn", "v_transposed": vt, "W": W, "H": 20, "T": 1500, "rc": r, "us": round(us.value, 1), "us_per_window": round(us.value / W, 1),
                       "TFs": round(tf, 1), "frac_tensor": round(tf / TF_PEAK, 3)}), flush=True)

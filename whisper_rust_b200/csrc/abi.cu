@@ -766,6 +766,17 @@ void whisper_b200_device_sync(struct whisper_context * ctx) {
     cudaStreamSynchronize(ctx->stream);
 }
 
+}  // extern "C" (closed around the device helper below)
+// pseudo-random f16 fill in [-1, 1) for the micro-benchmarks (constant operands would under-state switching power)
+__global__ void bench_fill_f16_kernel(__half * p, size_t n, uint32_t seed) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        uint32_t x = (uint32_t) i * 2654435761u + seed;
+        x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+        p[i] = __float2half_rn((float) (int32_t) x * (1.0f / 2147483648.0f));
+    }
+}
+static void bench_fill_f16(void * p, size_t n, uint32_t seed) { bench_fill_f16_kernel<<<1184, 256>>>((__half *) p, n, seed); }
+extern "C" {
 int whisper_b200_test_gemm(const void * a, const void * b, void * c, int m, int n, int k, int lda, int ldb, int ldc, int c_is_f16,
                            const float * bias, int block_n) {
     WB_TRY
@@ -805,8 +816,8 @@ int whisper_b200_bench_gemm(int m, int n, int k, int c_is_f16, int flags, int bl
     bool ok = cudaMalloc((void **) &a, (size_t) m * k * 2) == cudaSuccess && cudaMalloc((void **) &b, wsz * n_weights * 2) == cudaSuccess &&
               cudaMalloc(&c, (size_t) m * n * 4) == cudaSuccess && cudaMalloc((void **) &bias, (size_t) n * 4) == cudaSuccess;
     if (ok) {
-        cudaMemset(a, 0x11, (size_t) m * k * 2);
-        cudaMemset(b, 0x11, wsz * n_weights * 2);
+        bench_fill_f16(a, (size_t) m * k, 1u);
+        bench_fill_f16(b, wsz * n_weights, 2u);
         cudaMemset(c, 0, (size_t) m * n * 4);
         cudaMemset(bias, 0, (size_t) n * 4);
     }
@@ -840,14 +851,14 @@ int whisper_b200_bench_gemm(int m, int n, int k, int c_is_f16, int flags, int bl
     WB_CATCH(3)
 }
 // fused encoder attention on device buffers: q, k, v f16 [W][H][T][64] (plain layout; repacked here into the kernel's panels)
-int whisper_b200_test_enc_attn(const void * q, const void * k, const void * v, void * out, int W, int H, int T) {
+int whisper_b200_test_enc_attn(const void * q, const void * k, const void * v, void * out, int W, int H, int T, int v_transposed) {
     WB_TRY
     const int R = W * T, Tpad = (int) pad_to(T, 8), S = H * 64;
     __half *qk = nullptr, *vT = nullptr;
-    if (cudaMalloc((void **) &qk, (size_t) 2 * H * R * 64 * 2) != cudaSuccess) return 1;
+    if (cudaMalloc((void **) &qk, (size_t) 3 * H * R * 64 * 2) != cudaSuccess) return 1;
     if (cudaMalloc((void **) &vT, (size_t) H * W * 64 * Tpad * 2) != cudaSuccess) { cudaFree(qk); return 1; }
     cudaMemset(vT, 0, (size_t) H * W * 64 * Tpad * 2);
-    std::vector<__half> hq((size_t) W * H * T * 64), hk(hq.size()), hv(hq.size()), pqk((size_t) 2 * H * R * 64), pv((size_t) H * W * 64 * Tpad);
+    std::vector<__half> hq((size_t) W * H * T * 64), hk(hq.size()), hv(hq.size()), pqk((size_t) 3 * H * R * 64), pv((size_t) H * W * 64 * Tpad);
     cudaMemcpy(hq.data(), q, hq.size() * 2, cudaMemcpyDeviceToHost);
     cudaMemcpy(hk.data(), k, hk.size() * 2, cudaMemcpyDeviceToHost);
     cudaMemcpy(hv.data(), v, hv.size() * 2, cudaMemcpyDeviceToHost);
@@ -859,29 +870,31 @@ int whisper_b200_test_enc_attn(const void * q, const void * k, const void * v, v
                     const size_t src = (((size_t) w * H + h) * T + t) * 64 + d;
                     pqk[((size_t) h * R + (size_t) w * T + t) * 64 + d] = hq[src];
                     pqk[((size_t) (H + h) * R + (size_t) w * T + t) * 64 + d] = hk[src];
+                    pqk[((size_t) (2 * H + h) * R + (size_t) w * T + t) * 64 + d] = hv[src];
                     pv[(((size_t) h * W + w) * 64 + d) * Tpad + t] = hv[src];
                 }
     cudaMemcpy(qk, pqk.data(), pqk.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(vT, pv.data(), pv.size() * 2, cudaMemcpyHostToDevice);
-    const bool ok = enc_attention(qk, vT, (__half *) out, W, T, Tpad, H, S, 0.125f, 0) && cudaDeviceSynchronize() == cudaSuccess;
+    const bool ok = enc_attention(qk, v_transposed ? vT : nullptr, (__half *) out, W, T, Tpad, H, S, 0.125f, 0) && cudaDeviceSynchronize() == cudaSuccess;
     cudaFree(qk); cudaFree(vT);
     return ok ? 0 : 2;
     WB_CATCH(3)
 }
 // micro-benchmark of the fused encoder attention: W windows x H heads x T frames; returns microseconds per launch
-int whisper_b200_bench_enc_attn(int W, int H, int T, int iters, double * us_per_launch) {
+int whisper_b200_bench_enc_attn(int W, int H, int T, int iters, int v_transposed, double * us_per_launch) {
     WB_TRY
     const int R = W * T, Tpad = (int) pad_to(T, 8), S = H * 64;
     __half *qk = nullptr, *vT = nullptr, *out = nullptr;
-    bool ok = cudaMalloc((void **) &qk, (size_t) 2 * H * R * 64 * 2) == cudaSuccess && cudaMalloc((void **) &vT, (size_t) H * W * 64 * Tpad * 2) == cudaSuccess &&
+    bool ok = cudaMalloc((void **) &qk, (size_t) 3 * H * R * 64 * 2) == cudaSuccess && cudaMalloc((void **) &vT, (size_t) H * W * 64 * Tpad * 2) == cudaSuccess &&
               cudaMalloc((void **) &out, (size_t) R * S * 2) == cudaSuccess;
-    if (ok) { cudaMemset(qk, 0x11, (size_t) 2 * H * R * 64 * 2); cudaMemset(vT, 0x11, (size_t) H * W * 64 * Tpad * 2); }
+    if (ok) { bench_fill_f16(qk, (size_t) 3 * H * R * 64, 3u); bench_fill_f16(vT, (size_t) H * W * 64 * Tpad, 4u); }
+    const __half * vt_arg = v_transposed ? vT : nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     ok = ok && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
-    for (int i = 0; i < 2 && ok; ++i) ok = enc_attention(qk, vT, out, W, T, Tpad, H, S, 0.125f, 0);
+    for (int i = 0; i < 2 && ok; ++i) ok = enc_attention(qk, vt_arg, out, W, T, Tpad, H, S, 0.125f, 0);
     if (ok) {
         cudaEventRecord(e0, 0);
-        for (int i = 0; i < iters && ok; ++i) ok = enc_attention(qk, vT, out, W, T, Tpad, H, S, 0.125f, 0);
+        for (int i = 0; i < iters && ok; ++i) ok = enc_attention(qk, vt_arg, out, W, T, Tpad, H, S, 0.125f, 0);
         cudaEventRecord(e1, 0);
         ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
         float ms = 0.0f;

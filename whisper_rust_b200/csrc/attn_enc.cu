@@ -38,6 +38,9 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// kVRow = true : V in the same per-head [t][64] panels as Q and K (panel 2H + h): the P.V MMA reads it as an MN-major B operand
+// kVRow = false: V^T panels [H][W][64][Tpad] (K-major B operand)
+template <bool kVRow>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_constant__ CUtensorMap tmap_vt, __half * __restrict__ out,
                 int T, int R, int H, int W, int S, float scale_log2e) {
@@ -111,15 +114,20 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
                 const int st = j % AT_NV;
                 mbar_wait(v_empty + st, ((j / AT_NV) & 1) ^ 1);
                 mbar_expect_tx(v_full + st, AT_TILE);
-                tma_load_2d(v_smem + st * AT_TILE, &tmap_vt, v_full + st, j * AT_KV, v_row);                   // kv [0,64) of the tile
-                tma_load_2d(v_smem + st * AT_TILE + AT_TILE / 2, &tmap_vt, v_full + st, j * AT_KV + 64, v_row);  // kv [64,128)
+                if constexpr (kVRow) {
+                    tma_load_2d(v_smem + st * AT_TILE, &tmap_qk, v_full + st, 0, (2 * H + h) * R + w * T + j * AT_KV);  // [128 kv][64 d]
+                } else {
+                    tma_load_2d(v_smem + st * AT_TILE, &tmap_vt, v_full + st, j * AT_KV, v_row);                   // kv [0,64) of the tile
+                    tma_load_2d(v_smem + st * AT_TILE + AT_TILE / 2, &tmap_vt, v_full + st, j * AT_KV + 64, v_row);  // kv [64,128)
+                }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------- MMA issuer ---------------------------------------------
         if (elect_one()) {
             constexpr uint32_t idesc_s = umma_idesc_f16(128, 128);
-            constexpr uint32_t idesc_o = umma_idesc_f16(128, 64);
+            // bit 16 of the instruction descriptor: B operand is MN-major (rows of V are kv = the reduction index)
+            constexpr uint32_t idesc_o = umma_idesc_f16(128, 64) | (kVRow ? (1u << 16) : 0u);
             const uint32_t q_addr = smem_u32(q_smem), p_addr = smem_u32(p_smem), k_addr = smem_u32(k_smem), v_addr = smem_u32(v_smem);
             mbar_wait(q_full, 0);
             int sn = 0;  // S tiles issued so far (pass A: 0..nkv-1, pass B: nkv..2nkv-1)
@@ -150,10 +158,12 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
                         const uint64_t dp = umma_desc_k_sw128(p_addr + (g * 2 + hh) * AT_TILE);
+                        // K-major V^T: 32 bytes per 16-kv step inside the 128-byte row; MN-major V: 16 rows x 128 bytes per step
                         const uint64_t dv = umma_desc_k_sw128(v_addr + st * AT_TILE + hh * (AT_TILE / 2));
+                        constexpr uint64_t vstep = kVRow ? (16 * 128) >> 4 : 2;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_f16_ss(tmem_base + 256 + g * 64, dp + (uint64_t) (2 * k), dv + (uint64_t) (2 * k), idesc_o, (j | hh | k) != 0);
+                            umma_f16_ss(tmem_base + 256 + g * 64, dp + (uint64_t) (2 * k), dv + vstep * (uint64_t) k, idesc_o, (j | hh | k) != 0);
                     }
                     umma_commit(p_empty + g);
                 }
@@ -266,21 +276,26 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
 static std::atomic<uint64_t> g_attn_launches{0};
 uint64_t enc_attn_launch_count() { return g_attn_launches.load(); }
 
-// qk: f16 per-head panels [2H][R][64] (Q heads then K heads, R = W*T rows); vT: f16 [H][W][64][Tpad]; out: f16 [R][S]
+// qk: f16 per-head panels [2H][R][64] (Q heads then K heads, R = W*T rows) followed, when vT == nullptr, by the V heads
+// ([3H][R][64]); otherwise vT: f16 [H][W][64][Tpad]; out: f16 [R][S]
 bool enc_attention(const __half * qk, const __half * vT, __half * out, int W, int T, int Tpad, int H, int S, float scale, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         attr_set = true;
     }
     const int R = W * T;
+    const bool vrow = vT == nullptr;
     CUtensorMap tq, tv;
-    if (!tmap_encode_2d(&tq, qk, 64, (uint64_t) 2 * H * R, 64, 64, 128)) return false;
-    if (!tmap_encode_2d(&tv, vT, (uint64_t) Tpad, (uint64_t) H * W * 64, (uint64_t) Tpad, 64, 64)) return false;
+    if (!tmap_encode_2d(&tq, qk, 64, (uint64_t) (vrow ? 3 : 2) * H * R, 64, 64, 128)) return false;
+    if (vrow) tv = tq;
+    else if (!tmap_encode_2d(&tv, vT, (uint64_t) Tpad, (uint64_t) H * W * 64, (uint64_t) Tpad, 64, 64)) return false;
     dim3 grid(ceil_div(T, 256), H, W);
     const double flops = 4.0 * (double) T * T * 64 * H * W;
     ProfScope prof_scope(PC_ENC_SOFTMAX, stream, (double) R * S * 2 * 4, flops);
-    enc_attn_kernel<<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, scale * 1.4426950408889634f);
+    if (vrow) enc_attn_kernel<true><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, scale * 1.4426950408889634f);
+    else enc_attn_kernel<false><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, scale * 1.4426950408889634f);
     WB_CUDA_OK(cudaGetLastError());
     g_attn_launches.fetch_add(1);
     return true;

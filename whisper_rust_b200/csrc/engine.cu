@@ -311,7 +311,7 @@ static bool ensure_enc_ws(Context & ctx, int windows, int T) {
     };
     const size_t R = (size_t) W * T;
     const size_t o_melT = take((size_t) W * (2 * T + 2) * m.kc1 * 2), o_h1 = take((size_t) W * (2 * T + 2) * S * 2);
-    const size_t o_x = take(R * S * 4), o_xa = take(R * S * 2), o_qk = take(2 * R * S * 2);
+    const size_t o_x = take(R * S * 4), o_xa = take(R * S * 2), o_qk = take(3 * R * S * 2);  // Q, K (, V) per-head panels
     const bool legacy = legacy_attention();
     const size_t o_vT = take((size_t) H * W * 64 * Tpad * 2), o_sc = take(legacy ? (size_t) H * W * T * Tpad * 4 : 16);
     const size_t o_p = take(legacy ? (size_t) H * W * T * Tpad * 2 : 16), o_att = take(R * S * 2), o_hb = take(R * 4 * S * 2);
@@ -485,6 +485,14 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
     for (int il = 0; il < L; ++il) {
         const EncLayer & l = m.enc[il];
         if (!layernorm_rows(ws.x, R, S, l.ln1.g, l.ln1.b, hp.eps, ws.xa, nullptr, s)) return false;
+        if (!legacy_attention()) {
+            // Q (bias), K (no bias), V (bias) in ONE GEMM -> f16 per-head [t][64] panels [3H][R][64]  (wc:2131-2148; the f16 casts of
+            // wc:2183-2200 are the epilogue's rounding)
+            GemmEpilogue e{};
+            e.out = ws.qk; e.out_f16 = 1; e.out_mode = OUT_HEAD; e.head_stride = (int64_t) R * 64; e.batch_div = 1;
+            e.bias = l.qk.b;
+            if (!gemm_f16_tc(opnd(ws.xa, R, S), opnd(l.qk.w, 3 * S, S), R, 3 * S, S, 1, e, 0, s)) return false;
+        } else {
         {   // Q (with bias) and K (no bias) -> per-head [t][64] panels, f16 (the casts of wc:2183-2186 and mul_mat's f32->f16)
             GemmEpilogue e{};
             e.out = ws.qk; e.out_f16 = 1; e.out_mode = OUT_HEAD; e.head_stride = (int64_t) R * 64; e.batch_div = 1;
@@ -498,9 +506,10 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
             e.bias = l.v.b;
             if (!gemm_f16_tc(opnd(ws.xa, R, S), opnd(l.v.w, S, S), R, S, S, 1, e, 0, s)) return false;
         }
+        }
         if (!legacy_attention()) {
             // fused: softmax(Q K^T * D^-1/2) V with the scores in TMEM (wc:2183-2206)
-            if (!enc_attention(ws.qk, ws.vT, ws.att, W, T, Tpad, H, S, kq_scale, s)) return false;
+            if (!enc_attention(ws.qk, nullptr, ws.att, W, T, Tpad, H, S, kq_scale, s)) return false;
         } else {
         {   // scores = Q K^T per (head, window)  (wc:2189)
             GemmEpilogue e = epi_row(ws.sc, false, Tpad);

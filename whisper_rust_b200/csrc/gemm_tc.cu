@@ -377,7 +377,7 @@ gemm_f16_persist_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     } else {
         // ---------------- epilogue warps 2..5: TMEM lane quadrant = warp % 4 ----------------
         const int grp = warp & 3;
-        uint8_t * my_buf = epi_smem + grp * 2 * kEpiBufBytes;
+        uint8_t * my_buf  = epi_smem + grp * 2 * kEpiBufBytes;
         const uint32_t row_off = (uint32_t) lane * 128u;
         const uint32_t sw = (uint32_t) (lane & 7);
         int acc = 0, buf = 0;
@@ -387,6 +387,7 @@ gemm_f16_persist_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
             const int m0 = ((t / n_tiles) % m_tiles) * BLOCK_M;
             const int b  = t / (n_tiles * m_tiles);
             const int mw = m0 + grp * 32;  // first row of this warp's slab
+
             const float * bias = epi.bias ? epi.bias + (int64_t) b * epi.bias_batch_stride : nullptr;
 
             mbar_wait(tmem_full + acc, acc_phase);
@@ -406,38 +407,49 @@ gemm_f16_persist_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
                             tmem_ld_32x32(t_acc + (uint32_t) (c * kChunkCols + 32), r1);
                         }
                     }
-                    // bias values of this chunk: lane j holds column nc + j (and nc + 32 + j)
-                    float bv0 = 0.0f, bv1 = 0.0f;
-                    if (bias != nullptr) {
-                        if (nc + lane < N) bv0 = __ldg(bias + nc + lane);
-                        if (kF16 && nc + 32 + lane < N) bv1 = __ldg(bias + nc + 32 + lane);
-                    }
-                    tmem_ld_wait();
-                    float v[kChunkCols];
+                    // bias of this chunk's columns: the same address in every lane (one broadcast transaction per load, L1-resident)
+                    float4 bsrc[kChunkCols / 4];
+                    if (bias != nullptr && nc + kChunkCols <= N) {
 #pragma unroll
-                    for (int j = 0; j < kChunkCols; ++j) {
-                        float x = __uint_as_float(r[j]);
-                        if (bias != nullptr) x = __fadd_rn(x, __shfl_sync(0xffffffffu, j < 32 ? bv0 : bv1, j & 31));
-                        const int n = nc + j;
-                        if (n >= epi.scale_n0 && n < epi.scale_n1) x = __fmul_rn(x, epi.scale);
-                        v[j] = x;
+                        for (int q = 0; q < kChunkCols / 4; ++q) bsrc[q] = __ldg((const float4 *) (bias + nc) + q);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < kChunkCols / 4; ++q) {
+                            bsrc[q].x = (bias != nullptr && nc + q * 4 + 0 < N) ? __ldg(bias + nc + q * 4 + 0) : 0.0f;
+                            bsrc[q].y = (bias != nullptr && nc + q * 4 + 1 < N) ? __ldg(bias + nc + q * 4 + 1) : 0.0f;
+                            bsrc[q].z = (bias != nullptr && nc + q * 4 + 2 < N) ? __ldg(bias + nc + q * 4 + 2) : 0.0f;
+                            bsrc[q].w = (bias != nullptr && nc + q * 4 + 3 < N) ? __ldg(bias + nc + q * 4 + 3) : 0.0f;
+                        }
                     }
+                    // column-range scale: the range is aligned to the chunk width (checked on the host)
+                    const float sc = (nc >= epi.scale_n0 && nc < epi.scale_n1) ? epi.scale : 1.0f;
                     // the TMA store issued two chunks ago from this buffer must have finished reading it
                     if (lane == 0) bulk_wait_group_read<1>();
+                    tmem_ld_wait();
                     __syncwarp();
                     uint8_t * dst = my_buf + buf * kEpiBufBytes + row_off;
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         uint4 pk;
                         if constexpr (kF16) {
-                            __half2 h0 = __floats2half2_rn(v[q * 8 + 0], v[q * 8 + 1]);
-                            __half2 h1 = __floats2half2_rn(v[q * 8 + 2], v[q * 8 + 3]);
-                            __half2 h2 = __floats2half2_rn(v[q * 8 + 4], v[q * 8 + 5]);
-                            __half2 h3 = __floats2half2_rn(v[q * 8 + 6], v[q * 8 + 7]);
+                            const float4 b0 = bsrc[q * 2], b1 = bsrc[q * 2 + 1];  // same address in every lane: broadcast
+                            const float v0 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 0]), b0.x), sc);
+                            const float v1 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 1]), b0.y), sc);
+                            const float v2 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 2]), b0.z), sc);
+                            const float v3 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 3]), b0.w), sc);
+                            const float v4 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 4]), b1.x), sc);
+                            const float v5 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 5]), b1.y), sc);
+                            const float v6 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 6]), b1.z), sc);
+                            const float v7 = __fmul_rn(__fadd_rn(__uint_as_float(r[q * 8 + 7]), b1.w), sc);
+                            __half2 h0 = __floats2half2_rn(v0, v1), h1 = __floats2half2_rn(v2, v3);
+                            __half2 h2 = __floats2half2_rn(v4, v5), h3 = __floats2half2_rn(v6, v7);
                             pk.x = *(uint32_t *) &h0; pk.y = *(uint32_t *) &h1; pk.z = *(uint32_t *) &h2; pk.w = *(uint32_t *) &h3;
                         } else {
-                            pk.x = __float_as_uint(v[q * 4 + 0]); pk.y = __float_as_uint(v[q * 4 + 1]);
-                            pk.z = __float_as_uint(v[q * 4 + 2]); pk.w = __float_as_uint(v[q * 4 + 3]);
+                            const float4 b0 = bsrc[q];
+                            pk.x = __float_as_uint(__fmul_rn(__fadd_rn(__uint_as_float(r[q * 4 + 0]), b0.x), sc));
+                            pk.y = __float_as_uint(__fmul_rn(__fadd_rn(__uint_as_float(r[q * 4 + 1]), b0.y), sc));
+                            pk.z = __float_as_uint(__fmul_rn(__fadd_rn(__uint_as_float(r[q * 4 + 2]), b0.z), sc));
+                            pk.w = __float_as_uint(__fmul_rn(__fadd_rn(__uint_as_float(r[q * 4 + 3]), b0.w), sc));
                         }
                         *(uint4 *) (dst + (((uint32_t) q ^ sw) << 4)) = pk;
                     }
@@ -617,6 +629,8 @@ static bool persist_eligible(const GemmEpilogue & e, const GemmTaps & taps, int 
     if (e.out_mode == OUT_ROW && (((e.ldo * es) & 15) != 0 || e.ldo < N)) return false;
     if (e.out_mode == OUT_HEAD && (!e.out_f16 || (N & 63) != 0 || ((e.head_stride * es) & 15) != 0)) return false;
     if (batch > 1 && ((e.out_batch_stride * es) & 15) != 0) return false;
+    if (e.bias != nullptr && ((((uintptr_t) e.bias) & 15) != 0 || (batch > 1 && (e.bias_batch_stride & 3) != 0))) return false;
+    if (e.scale_n1 > e.scale_n0 && ((e.scale_n0 | e.scale_n1) & 63) != 0) return false;  // the epilogue scales whole 64-column chunks
     if (e.res != nullptr) {  // only the in-place residual  out += ...
         if (e.res != (const float *) e.out || e.out_f16 || e.out_mode != OUT_ROW || e.ldr != e.ldo || e.res_row_mod != 0) return false;
         if (batch > 1 && e.res_batch_stride != e.out_batch_stride) return false;

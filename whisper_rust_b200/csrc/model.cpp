@@ -227,8 +227,10 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     WANT(m.e_ln.g, S); WANT(m.e_ln.b, S);
     for (auto & l : m.enc) {
         WANT(l.ln1.g, S); WANT(l.ln1.b, S); WANT(l.ln2.g, S); WANT(l.ln2.b, S);
-        WANT(l.qk.w, (size_t) 2 * S * S); WANT(l.qk.b, 2 * S);
-        WANT(l.v.w, (size_t) S * S); WANT(l.v.b, S);
+        // query, key, value rows contiguous ([3S][S], bias (bq, 0, bv)): one GEMM launch produces all three
+        // (2*S*S*2 and 2*S*4 bytes are multiples of the 256-byte slot size for every Whisper width; checked after allocation)
+        WANT(l.qk.w, (size_t) 2 * S * S); WANT(l.v.w, (size_t) S * S);
+        WANT(l.qk.b, 2 * S); WANT(l.v.b, S);
         WANT(l.o.w, (size_t) S * S); WANT(l.o.b, S);
         WANT(l.fc1.w, (size_t) 4 * S * S); WANT(l.fc1.b, 4 * S);
         WANT(l.fc2.w, (size_t) 4 * S * S); WANT(l.fc2.b, S);
@@ -255,6 +257,10 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     WB_CUDA_OK(cudaMalloc((void **) &m.arena, m.arena_size));
     WB_CUDA_OK(cudaMemset(m.arena, 0, m.arena_size));  // fused-bias gaps (key projections have no bias) stay 0
     for (auto & s : slots) *s.pp = m.arena + s.off;
+    for (auto & l : m.enc) {
+        WB_CHECK(l.v.w == l.qk.w + (size_t) 2 * S * S && l.v.b == l.qk.b + 2 * S,
+                 "encoder Q/K/V weights are not contiguous in the arena (n_audio_state %d)\n", S);
+    }
 
     // ---------------- tables ----------------
     {
