@@ -761,7 +761,9 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
         if (!gemm_f16_tc(opnd(a_rows, n_flag, S), opnd(m.d_te, V, S), n_flag, V, S, 1, e, 0, s)) return false;
     }
     // timing buckets of the reference (wc:2982-2991) per state
-    const int64_t dt = time_us() - t0;
+    int n_states = 0;
+    for (int i = 0; i < n; ++i) n_states += (i == 0 || rows[i].st != rows[i - 1].st) ? 1 : 0;
+    const int64_t dt = (time_us() - t0) / std::max(1, n_states);  // a batched call is shared by its states
     for (int i = 0; i < n;) {
         State * st = rows[i].st;
         int cnt = 1;
