@@ -72,6 +72,10 @@ WHISPER_API int whisper_b200_test_cross_attn(const void * q_f16, const void * kv
  * force_split: 0 auto split-K, 1 direct epilogue, >1 that many k-splits */
 WHISPER_API int whisper_b200_test_gemm_wstream(const void * w_f16, const void * x_f16, float * out, int n, int n_out, int k, const float * bias,
                                                int force_split);
+/* decode-step GEMM with the split-K reduction inside a thread-block cluster (distributed shared memory), n <= 256:
+ * mode 0: out f16 [n][n_out] = f16((x.w^T + bias) * (feature < scale_f1 ? scale : 1));  mode 1: out f32 [n][n_out] += x.w^T + bias */
+WHISPER_API int whisper_b200_test_gemm_wcluster(const void * w_f16, const void * x_f16, void * out, int n, int n_out, int k, const float * bias,
+                                                int mode, float scale, int scale_f1);
 /* the TMA-streamed decode-step cross attention: same contract as whisper_b200_test_cross_attn */
 WHISPER_API int whisper_b200_test_cross_attn_step(const void * q_f16, const void * kv_f16, void * out_f16, int n_rows, int n_head, int n_ctx);
 /* micro-benchmarks, CUDA-event timed on the launching stream, graph-replayed so that launch overhead is excluded:

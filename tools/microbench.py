@@ -20,9 +20,10 @@ def run(kind, n, a, b, c, iters):
     print(json.dumps({"kind": kind, "n": n, "a": a, "b": b, "c": c, "rc": r, "us": round(us.value, 3), "GBs": round(gbs, 1), "frac_hbm": round(gbs / PEAK, 3)}), flush=True)
 for n in (1, 16, 64):
     run("cross_attn_step", n, 20, 1500, 8 if n > 16 else 32, 5)
-for n in (16, 64):
+for n in (16, 64, 256):
     for (no, k) in ((1280, 1280), (3840, 1280), (5120, 1280), (1280, 5120)):
         run("gemm_wstream", n, no, k, 48, 5)
+        run("gemm_wcluster", n, no, k, 48, 5)
 
 # encoder GEMM shapes at large-v3, W windows of 1500 rows (tensor roofline)
 g = lib.whisper_b200_bench_gemm

@@ -936,6 +936,12 @@ int whisper_b200_test_cross_attn(const void * q, const void * kv, void * out, in
     WB_CATCH(3)
 }
 
+int whisper_b200_test_gemm_wcluster(const void * w, const void * x, void * out, int n, int n_out, int k, const float * bias, int mode,
+                                    float scale, int scale_f1) {
+    WB_TRY
+    return test_gemm_wcluster((const __half *) w, (const __half *) x, out, n, n_out, k, bias, mode, scale, scale_f1, nullptr) ? 0 : 1;
+    WB_CATCH(3)
+}
 int whisper_b200_test_gemm_wstream(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int force_split) {
     WB_TRY
     return test_gemm_wstream((const __half *) w, (const __half *) x, out, n, n_out, k, bias, force_split) ? 0 : 1;
@@ -952,6 +958,7 @@ int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c
     bool ok = false;
     if (strcmp(kind, "cross_attn_step") == 0) ok = bench_cross_attn_step(n_rows, a /*H*/, b /*T*/, c /*layers*/, iters, &r);
     else if (strcmp(kind, "gemm_wstream") == 0) ok = bench_gemm_wstream(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
+    else if (strcmp(kind, "gemm_wcluster") == 0) ok = bench_gemm_wcluster(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
     if (!ok) return 1;
     if (us_per_launch) *us_per_launch = r.us_per_launch;
     if (bytes_per_launch) *bytes_per_launch = r.bytes_per_launch;

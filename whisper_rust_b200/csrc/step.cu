@@ -173,6 +173,199 @@ gemm_wstream_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     }
 }
 
+// =============================================================================================
+// gemm_wcluster: the same weight-streaming GEMM with the split-K reduction done INSIDE a thread-block cluster
+// =============================================================================================
+// grid (split, tiles), cluster (split, 1, 1): the CTAs of one cluster share a 128-feature weight tile and own disjoint
+// k-ranges.  Each CTA accumulates its partial D[128 features][n_pad tokens] in TMEM, spills it to its own shared memory
+// (over the dead pipeline stages) as P[token][128 features] f32, and after a cluster barrier CTA r reduces the token slice
+// [r * tpr, (r + 1) * tpr) by reading every peer's P through distributed shared memory in rank order 0..split-1 (the same
+// fixed summation order the split-K consumers used), applies the epilogue and writes the FINAL values: no partials in
+// global memory, no reduction work in the consumer kernels.
+//   WC_F16      out f16 = f16((acc + bias) * scale?)     scale for features < scale_f1   (wc:2558-2583 Q/K/V, wc:2700-2707 cross Q)
+//   WC_RESIDUAL x f32 = (acc + bias) + x                 in place                          (wc:2657-2664, 2771-2777, 2807-2814)
+//   WC_GELU     out f16 = f16(gelu_table[f16(acc + bias)])                                  (wc:2795-2802)
+enum WcMode : int { WC_F16 = 0, WC_RESIDUAL = 1, WC_GELU = 2 };
+struct WcArgs {
+    int n, n_pad, N_out;
+    int kb_total, kb_per_split, stages, split;
+    int mode;
+    void * out;
+    int64_t ldo;
+    const float * bias;
+    float scale;
+    int scale_f1;
+    const __half * gelu_table;
+    uint32_t tmem_cols;
+    int tok_per_rank;
+};
+
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t local_addr, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(remote) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(WS_THREADS, 1)
+gemm_wcluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, WcArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    const int b_bytes     = a.n_pad * 128;
+    const int stage_bytes = WS_A_BYTES + b_bytes;
+    const int main_bytes  = max(a.stages * stage_bytes, a.n_pad * 512);  // pipeline stages, later the partial tile P
+    uint64_t * full_bar   = (uint64_t *) (smem + main_bytes);
+    uint64_t * empty_bar  = full_bar + a.stages;
+    uint64_t * tmem_full  = empty_bar + a.stages;
+    uint32_t * tmem_slot  = (uint32_t *) (tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank  = (int) cluster_ctarank();  // == blockIdx.x: the split index
+    const int f0    = blockIdx.y * 128;
+    const int kb0   = rank * a.kb_per_split;
+    const int nkb   = min(a.kb_per_split, a.kb_total - kb0);  // >= 1 by construction of the plan
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_w);
+        tma_prefetch_desc(&tmap_x);
+        for (int s = 0; s < a.stages; ++s) {
+            mbar_init(full_bar + s, 1);
+            mbar_init(empty_bar + s, 1);
+        }
+        mbar_init(tmem_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc_rt(tmem_slot, a.tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint64_t pol_w = l2_policy_evict_first(), pol_x = l2_policy_evict_last();
+            const int pre = min(nkb, a.stages);
+            for (int i = 0; i < pre; ++i) {  // weights do not depend on the previous kernel
+                mbar_expect_tx(full_bar + i, stage_bytes);
+                tma_load_2d_hint(smem + i * stage_bytes, &tmap_w, full_bar + i, (kb0 + i) * 64, f0, pol_w);
+            }
+            pdl_wait();
+            for (int i = 0; i < pre; ++i)
+                tma_load_2d_hint(smem + i * stage_bytes + WS_A_BYTES, &tmap_x, full_bar + i, (kb0 + i) * 64, 0, pol_x);
+            int stage = pre == a.stages ? 0 : pre;
+            uint32_t phase = pre == a.stages ? 1 : 0;
+            for (int i = pre; i < nkb; ++i) {
+                mbar_wait(empty_bar + stage, phase ^ 1);
+                uint8_t * sa = smem + stage * stage_bytes;
+                mbar_expect_tx(full_bar + stage, stage_bytes);
+                tma_load_2d_hint(sa, &tmap_w, full_bar + stage, (kb0 + i) * 64, f0, pol_w);
+                tma_load_2d_hint(sa + WS_A_BYTES, &tmap_x, full_bar + stage, (kb0 + i) * 64, 0, pol_x);
+                if (++stage == a.stages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            const uint32_t idesc = umma_idesc_f16(128, (uint32_t) a.n_pad);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = 0; i < nkb; ++i) {
+                mbar_wait(full_bar + stage, phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+                const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + WS_A_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base, da + (uint64_t) (2 * k), db + (uint64_t) (2 * k), idesc, (i | k) != 0);
+                umma_commit(empty_bar + stage);
+                if (++stage == a.stages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            umma_commit(tmem_full);
+        }
+    } else {
+        // warps 2..5: spill the accumulator (lane = feature, column = token) to P[token][feature]; all MMAs have retired, so
+        // the pipeline stages underneath are dead
+        const int grp = warp & 3;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        float * P = (float *) smem + grp * 32 + lane;
+#pragma unroll 1
+        for (int c0 = 0; c0 < a.n_pad; c0 += 16) {
+            if (c0 >= a.n) break;
+            uint32_t r[16];
+            tmem_ld_32x16(tmem_base + ((uint32_t) (grp * 32) << 16) + (uint32_t) c0, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) P[(c0 + j) * 128] = __uint_as_float(r[j]);
+        }
+        tc_fence_before();
+    }
+    __syncwarp();
+    cluster_sync_all();  // every CTA's P is complete and visible cluster-wide
+
+    if (warp >= 2) {
+        pdl_wait();  // the output may still be read by the previous kernel (every thread that writes global memory waits)
+        const int e  = (warp - 2) * 32 + lane;  // 0..127
+        const int fl = (e & 31) * 4;            // 4 consecutive features of the tile
+        const int f  = f0 + fl;
+        const int t0 = rank * a.tok_per_rank, t1 = min(a.n, t0 + a.tok_per_rank);
+        const uint32_t p_local = smem_u32(smem) + (uint32_t) fl * 4u;
+        float4 bias = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const bool f_ok = f < a.N_out;
+        if (a.bias != nullptr && f_ok) bias = __ldg((const float4 *) (a.bias + f));
+        const float sc = (f < a.scale_f1) ? a.scale : 1.0f;
+#pragma unroll 1
+        for (int t = t0 + (e >> 5); t < t1; t += 4) {
+            float4 v = ld_dsmem_f4(p_local + (uint32_t) t * 512u, 0);
+            for (int s = 1; s < a.split; ++s) {
+                const float4 w = ld_dsmem_f4(p_local + (uint32_t) t * 512u, (uint32_t) s);
+                v.x = __fadd_rn(v.x, w.x); v.y = __fadd_rn(v.y, w.y); v.z = __fadd_rn(v.z, w.z); v.w = __fadd_rn(v.w, w.w);
+            }
+            if (!f_ok) continue;
+            v.x = __fadd_rn(v.x, bias.x); v.y = __fadd_rn(v.y, bias.y); v.z = __fadd_rn(v.z, bias.z); v.w = __fadd_rn(v.w, bias.w);
+            if (a.mode == WC_RESIDUAL) {
+                float4 * xp = (float4 *) ((float *) a.out + (int64_t) t * a.ldo + f);
+                const float4 x = *xp;
+                v.x = __fadd_rn(v.x, x.x); v.y = __fadd_rn(v.y, x.y); v.z = __fadd_rn(v.z, x.z); v.w = __fadd_rn(v.w, x.w);
+                *xp = v;
+            } else {
+                if (a.mode == WC_GELU) {
+                    v.x = gelu_f16table(v.x, a.gelu_table); v.y = gelu_f16table(v.y, a.gelu_table);
+                    v.z = gelu_f16table(v.z, a.gelu_table); v.w = gelu_f16table(v.w, a.gelu_table);
+                } else {
+                    v.x = __fmul_rn(v.x, sc); v.y = __fmul_rn(v.y, sc); v.z = __fmul_rn(v.z, sc); v.w = __fmul_rn(v.w, sc);
+                }
+                const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+                uint2 pk;
+                pk.x = *(const uint32_t *) &h0;
+                pk.y = *(const uint32_t *) &h1;
+                *(uint2 *) ((__half *) a.out + (int64_t) t * a.ldo + f) = pk;
+            }
+        }
+    }
+    __syncwarp();
+    cluster_sync_all();  // no CTA may exit (and release its shared memory) while a peer is still reading it
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_rt(tmem_base, a.tmem_cols);
+    }
+}
+
 // ---- host side: plan (split / stages) and launch --------------------------------------------------------------
 static std::atomic<uint64_t> g_step_launches{0};
 static bool g_pdl = true;  // launch with programmatic stream serialization (WB200_NO_PDL=1 switches it off)
@@ -258,6 +451,75 @@ static bool gemm_wstream(const __half * W, const __half * X, int n, int N_out, i
     return launch_k(gemm_wstream_kernel, dim3(p.tiles, p.split), dim3(WS_THREADS), (size_t) p.smem, s, pdl, tw, tx, a);
 }
 
+// ---- gemm_wcluster: plan and launch ---------------------------------------------------------------------------------
+struct WcPlan {
+    int tiles, split, kb_total, kb_per_split, stages, n_pad, smem, tok_per_rank;
+    uint32_t tmem_cols;
+};
+static WcPlan wc_plan(int n, int N_out, int K) {
+    WcPlan p{};
+    p.tiles    = ceil_div(N_out, 128);
+    p.kb_total = ceil_div(K, 64);
+    p.n_pad    = (int) pad_to(std::max(n, 1), 16);
+    // ~one CTA per SM, clusters of at most 8 (the portable limit), at least two k-blocks per CTA
+    int split = std::max(1, std::min(8, 148 / p.tiles));
+    split = std::min(split, std::max(1, p.kb_total / 2));
+    p.kb_per_split = ceil_div(p.kb_total, split);
+    p.split        = ceil_div(p.kb_total, p.kb_per_split);
+    p.tok_per_rank = ceil_div(n, p.split);
+    const int stage_bytes = WS_A_BYTES + p.n_pad * 128;
+    p.stages = std::max(1, std::min(std::min(4, p.kb_per_split), (192 * 1024) / stage_bytes));
+    p.smem   = std::max(p.stages * stage_bytes, p.n_pad * 512) + 1024 + 256;
+    uint32_t c = 32;
+    while ((int) c < p.n_pad) c <<= 1;
+    p.tmem_cols = c;
+    return p;
+}
+
+struct WcOut {
+    int mode = WC_F16;
+    void * out = nullptr;
+    int64_t ldo = 0;
+    const float * bias = nullptr;
+    float scale = 1.0f;
+    int scale_f1 = 0;
+    const __half * gelu_table = nullptr;
+};
+
+static bool gemm_wcluster(const __half * W, const __half * X, int n, int N_out, int K, const WcOut & o, cudaStream_t s, bool pdl) {
+    WB_CHECK(n >= 1 && n <= 256 && (N_out % 4) == 0, "gemm_wcluster handles 1..256 token rows, N_out %% 4 == 0 (got %d, %d)\n", n, N_out);
+    const WcPlan p = wc_plan(n, N_out, K);
+    static bool attr_set = false;
+    if (!attr_set) {
+        WB_CUDA_OK(cudaFuncSetAttribute(gemm_wcluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    WB_CHECK(p.smem <= 200 * 1024, "gemm_wcluster: %d bytes of shared memory\n", p.smem);
+    CUtensorMap tw, tx;
+    if (!tmap_encode_2d(&tw, W, (uint64_t) K, (uint64_t) N_out, (uint64_t) K, 64, 128)) return false;
+    if (!tmap_encode_2d(&tx, X, (uint64_t) K, (uint64_t) n, (uint64_t) K, 64, (uint32_t) p.n_pad)) return false;
+    WcArgs a{};
+    a.n = n; a.n_pad = p.n_pad; a.N_out = N_out;
+    a.kb_total = p.kb_total; a.kb_per_split = p.kb_per_split; a.stages = p.stages; a.split = p.split;
+    a.mode = o.mode; a.out = o.out; a.ldo = o.ldo; a.bias = o.bias; a.scale = o.scale; a.scale_f1 = o.scale_f1;
+    a.gelu_table = o.gelu_table; a.tmem_cols = p.tmem_cols; a.tok_per_rank = p.tok_per_rank;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(p.split, p.tiles);
+    cfg.blockDim = dim3(WS_THREADS);
+    cfg.dynamicSmemBytes = (size_t) p.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = p.split; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = (pdl && g_pdl) ? 2 : 1;
+    WB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_wcluster_kernel, tw, tx, a));
+    g_step_launches.fetch_add(1);
+    return true;
+}
+
 // =============================================================================================
 // ln_reduce: x = [residual | embedding] (+ bias + sum of split-K partials);  xa = f16(LayerNorm(x) * gamma + beta)
 // =============================================================================================
@@ -300,8 +562,16 @@ __global__ void __launch_bounds__(LN_THREADS)
 ln_reduce_kernel(LnArgs a) {
     __shared__ double red[8];
     pdl_launch_dependents();
-    pdl_wait();
     const int row = blockIdx.x, tid = threadIdx.x, S = a.S;
+    // parameters do not depend on the previous kernel: fetch them while it drains
+    float gm[LN_MAX_PER_THREAD], bt[LN_MAX_PER_THREAD];
+#pragma unroll
+    for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
+        const int i = tid + q * LN_THREADS;
+        gm[q] = i < S ? __ldg(a.gamma + i) : 0.0f;
+        bt[q] = i < S ? __ldg(a.beta + i) : 0.0f;
+    }
+    pdl_wait();
     float v[LN_MAX_PER_THREAD];
     double sum = 0.0;
     // split-K partials first: all loads of a split are independent, four splits are kept in flight
@@ -325,7 +595,7 @@ ln_reduce_kernel(LnArgs a) {
             if (a.te != nullptr) x = __fadd_rn(__half2float(a.te[(int64_t) a.tokens[row] * S + i]), a.pe[(int64_t) a.pos[row] * S + i]);
             else x = a.res[(int64_t) row * S + i];
             if (a.partial != nullptr) x = __fadd_rn(__fadd_rn(v[q], __ldg(a.bias + i)), x);
-            a.x_out[(int64_t) row * S + i] = x;
+            if (a.partial != nullptr || a.te != nullptr) a.x_out[(int64_t) row * S + i] = x;
             sum += (double) x;
         }
         v[q] = x;
@@ -348,7 +618,7 @@ ln_reduce_kernel(LnArgs a) {
     for (int q = 0; q < LN_MAX_PER_THREAD; ++q) {
         const int i = tid + q * LN_THREADS;
         if (i < S) {
-            const float y = __fadd_rn(__fmul_rn(__fmul_rn(v[q], scale), __ldg(a.gamma + i)), __ldg(a.beta + i));
+            const float y = __fadd_rn(__fmul_rn(__fmul_rn(v[q], scale), gm[q]), bt[q]);
             a.xa_out[(int64_t) row * S + i] = __float2half_rn(y);
         }
     }
@@ -368,6 +638,7 @@ struct SelfArgs {
     const SelfKvRow * rows;
     int S, layer;
     __half * out;           // [n][S]
+    const __half * qkv16;   // alternative to partial: finished f16 Q|K|V [n][3S] (bias and D^-1/4 scale applied by the GEMM)
 };
 
 __global__ void __launch_bounds__(128)
@@ -385,12 +656,17 @@ self_attn_step_kernel(SelfArgs a) {
     __half * vb = r.v_base + (int64_t) a.layer * r.n_ctx * S + h * 64;
     for (int t = tid; t < 192; t += 128) {
         const int part = t >> 6, d = t & 63, col = part * S + h * 64 + d;
-        const float * p = a.partial + (int64_t) j * 3 * S + col;
-        float acc = p[0];
-        for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
-        acc = __fadd_rn(acc, __ldg(a.bias + col));
-        if (part < 2) acc = __fmul_rn(acc, a.scale);
-        const __half hv = __float2half_rn(acc);
+        __half hv;
+        if (a.qkv16 != nullptr) {
+            hv = a.qkv16[(int64_t) j * 3 * S + col];
+        } else {
+            const float * p = a.partial + (int64_t) j * 3 * S + col;
+            float acc = p[0];
+            for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
+            acc = __fadd_rn(acc, __ldg(a.bias + col));
+            if (part < 2) acc = __fmul_rn(acc, a.scale);
+            hv = __float2half_rn(acc);
+        }
         if (part == 0) s_q[d] = __half2float(hv);
         else if (part == 1) kb[(int64_t) r.store_cell * S + d] = hv;
         else vb[(int64_t) r.store_cell * S + d] = hv;
@@ -719,7 +995,9 @@ struct StepWs {
     __half * xa = nullptr;       // [n][S] LayerNorm output
     __half * att = nullptr;      // [n][S] attention output
     __half * hb = nullptr;       // [n][4S]
-    float * partial = nullptr;   // split-K partial sums
+    __half * qkv16 = nullptr;    // [n][3S] finished Q|K|V (cluster GEMM path)
+    __half * q16 = nullptr;      // [n][S] finished cross-attention query
+    float * partial = nullptr;   // split-K partial sums (WB200_STEP=partials path)
     float * logits = nullptr;    // [n][V]
     float * samp_work = nullptr; // [n][3][V]
     uint8_t * h_stage = nullptr; // pinned
@@ -787,11 +1065,12 @@ bool ensure_ws(Context & ctx, StepWs & ws, int n) {
     };
     const size_t o_x = take((size_t) cap * S * 4), o_xa = take((size_t) cap * S * 2), o_att = take((size_t) cap * S * 2);
     const size_t o_hb = take((size_t) cap * 4 * S * 2), o_part = take(max_part * 4), o_lg = take((size_t) cap * V * 4);
-    const size_t o_sw = take((size_t) cap * 3 * V * 4);
+    const size_t o_sw = take((size_t) cap * 3 * V * 4), o_qkv = take((size_t) cap * 3 * S * 2), o_q = take((size_t) cap * S * 2);
     WB_CUDA_OK(cudaMalloc((void **) &ws.base, off));
     ws.x = (float *) (ws.base + o_x); ws.xa = (__half *) (ws.base + o_xa); ws.att = (__half *) (ws.base + o_att);
     ws.hb = (__half *) (ws.base + o_hb); ws.partial = (float *) (ws.base + o_part); ws.logits = (float *) (ws.base + o_lg);
     ws.samp_work = (float *) (ws.base + o_sw);
+    ws.qkv16 = (__half *) (ws.base + o_qkv); ws.q16 = (__half *) (ws.base + o_q);
     ws.stage_bytes = stage_layout(cap).bytes;
     WB_CUDA_OK(cudaMallocHost((void **) &ws.h_stage, ws.stage_bytes));
     WB_CUDA_OK(cudaMalloc((void **) &ws.d_stage, ws.stage_bytes));
@@ -832,7 +1111,54 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
         return launch_k(ln_reduce_kernel, dim3(n), dim3(LN_THREADS), 0, s, !embed, a);
     };
     if (!ln(nullptr, 0, nullptr, true, L > 0 ? m.dec[0].ln1 : m.d_ln)) return false;
-    for (int il = 0; il < L; ++il) {
+    // WB200_STEP=partials: the earlier design (split-K partials in global memory, reduced by the consumer kernels)
+    static const bool use_partials = [] { const char * e = getenv("WB200_STEP"); return e && strcmp(e, "partials") == 0; }();
+    for (int il = 0; il < L && !use_partials; ++il) {
+        const DecLayer & l = m.dec[il];
+        {   // Q|K|V: bias, D^-1/4 on Q and K, f16 (wc:2558-2583)
+            WcOut o{};
+            o.mode = WC_F16; o.out = ws.qkv16; o.ldo = 3 * S; o.bias = l.qkv.b; o.scale = kq_scale; o.scale_f1 = 2 * S;
+            if (!gemm_wcluster(l.qkv.w, ws.xa, n, 3 * S, S, o, s, true)) return false;
+        }
+        {
+            SelfArgs a{};
+            a.qkv16 = ws.qkv16; a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
+            if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), (size_t) 5120 * 4, s, true, a)) return false;
+        }
+        {   // x += Wo.att + bo (wc:2657-2664)
+            WcOut o{};
+            o.mode = WC_RESIDUAL; o.out = ws.x; o.ldo = S; o.bias = l.o.b;
+            if (!gemm_wcluster(l.o.w, ws.att, n, S, S, o, s, true)) return false;
+        }
+        if (!ln(nullptr, 0, nullptr, false, l.lnc)) return false;
+        {   // cross-attention query, f16 (wc:2700-2707)
+            WcOut o{};
+            o.mode = WC_F16; o.out = ws.q16; o.ldo = S; o.bias = l.cq.b;
+            if (!gemm_wcluster(l.cq.w, ws.xa, n, S, S, o, s, true)) return false;
+        }
+        {
+            CrossArgs a{};
+            a.q_f16 = ws.q16; a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
+            a.stages = xs_stages;
+            if (!launch_k(cross_attn_step_kernel, dim3(H, n), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, xs_stages), s, true, a)) return false;
+        }
+        {
+            WcOut o{};
+            o.mode = WC_RESIDUAL; o.out = ws.x; o.ldo = S; o.bias = l.co.b;
+            if (!gemm_wcluster(l.co.w, ws.att, n, S, S, o, s, true)) return false;
+        }
+        if (!ln(nullptr, 0, nullptr, false, l.ln2)) return false;
+        {   // MLP: f16(gelu(W1.x + b1)) through the reference's f16 table, then x += W2.h + b2 (wc:2795-2814)
+            WcOut o{};
+            o.mode = WC_GELU; o.out = ws.hb; o.ldo = 4 * S; o.bias = l.fc1.b; o.gelu_table = m.gelu_table;
+            if (!gemm_wcluster(l.fc1.w, ws.xa, n, 4 * S, S, o, s, true)) return false;
+            WcOut o2{};
+            o2.mode = WC_RESIDUAL; o2.out = ws.x; o2.ldo = S; o2.bias = l.fc2.b;
+            if (!gemm_wcluster(l.fc2.w, ws.hb, n, S, 4 * S, o2, s, true)) return false;
+        }
+        if (!ln(nullptr, 0, nullptr, false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln)) return false;
+    }
+    for (int il = 0; il < L && use_partials; ++il) {
         const DecLayer & l = m.dec[il];
         int split = 1;
         WsOut po{};
@@ -1146,6 +1472,44 @@ bool bench_gemm_wstream(int n_rows, int N_out, int K, int n_weights, int iters, 
         out->bytes_per_launch = (double) wsz * 2 + (double) n_rows * K * 2 + (double) p.split * n_rows * N_out * 4;
     }
     cudaFree(w); cudaFree(x); cudaFree(part);
+    return ok;
+}
+// cluster split-K GEMM on raw device pointers.  mode 0: out f16 [n][N_out] = f16((x.w^T + bias) * (f < scale_f1 ? scale : 1));
+// mode 1: out f32 [n][N_out] += x.w^T + bias (in place);  mode 2: f16 GELU through `gelu_table` (65,536 f16 entries, device)
+bool test_gemm_wcluster(const __half * w, const __half * x, void * out, int n, int N_out, int K, const float * bias, int mode, float scale,
+                        int scale_f1, const __half * gelu_table) {
+    g_pdl = false;
+    WcOut o{};
+    o.mode = mode; o.out = out; o.ldo = N_out; o.bias = bias; o.scale = scale; o.scale_f1 = scale_f1; o.gelu_table = gelu_table;
+    if (!gemm_wcluster(w, x, n, N_out, K, o, 0, false)) return false;
+    WB_CUDA_OK(cudaDeviceSynchronize());
+    return true;
+}
+
+bool bench_gemm_wcluster(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out) {
+    g_pdl = getenv("WB200_NO_PDL") == nullptr;
+    __half *w = nullptr, *x = nullptr, *y = nullptr;
+    const size_t wsz = (size_t) N_out * K;
+    bool ok = cudaMalloc((void **) &w, wsz * n_weights * 2) == cudaSuccess && cudaMalloc((void **) &x, (size_t) n_rows * K * 2) == cudaSuccess &&
+              cudaMalloc((void **) &y, (size_t) n_rows * N_out * 2) == cudaSuccess;
+    if (ok) {
+        cudaMemset(w, 0x11, wsz * n_weights * 2);
+        cudaMemset(x, 0x11, (size_t) n_rows * K * 2);
+    }
+    WcOut o{};
+    o.mode = WC_F16; o.out = y; o.ldo = N_out;
+    if (ok) {
+        float ms = 0.0f;
+        ok = time_graph([&](cudaStream_t st) {
+            bool k = true;
+            for (int i = 0; i < n_weights && k; ++i) k = gemm_wcluster(w + wsz * i, x, n_rows, N_out, K, o, st, i > 0);
+            return k;
+        }, iters, &ms);
+        out->launches = iters * n_weights;
+        out->us_per_launch = 1e3 * ms / std::max(1, out->launches);
+        out->bytes_per_launch = (double) wsz * 2 + (double) n_rows * K * 2 + (double) n_rows * N_out * 2;
+    }
+    cudaFree(w); cudaFree(x); cudaFree(y);
     return ok;
 }
 }  // namespace wb

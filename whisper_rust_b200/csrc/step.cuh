@@ -37,6 +37,9 @@ bool bench_gemm_wstream(int n_rows, int N_out, int K, int n_weights, int iters, 
 
 // test hooks on raw device pointers
 bool test_gemm_wstream(const __half * w, const __half * x, float * out, int n, int N_out, int K, const float * bias, int force_split);
+bool test_gemm_wcluster(const __half * w, const __half * x, void * out, int n, int N_out, int K, const float * bias, int mode, float scale,
+                        int scale_f1, const __half * gelu_table);
+bool bench_gemm_wcluster(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out);
 bool test_cross_attn_step(const __half * q_f16, const __half * kv, __half * out, int n_rows, int H, int T);
 
 }  // namespace wb
