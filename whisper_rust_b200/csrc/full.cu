@@ -916,92 +916,147 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         j.init();
     }
 
-    std::vector<State *> enc_states;
-    std::vector<int> enc_offsets;
-    std::vector<FullJob *> enc_jobs;
-    std::vector<BatchRow> rows;
-    std::vector<SamplerRow> srows;
-    std::vector<Decoder *> sdecs;
-    std::vector<FullJob *> dev_jobs;
+    // ---- decode lanes (step.cuh): contiguous groups of jobs that advance independently.  A lane's fused decode step is
+    // launched without waiting; the host then serves the other lanes, so their kernels and this bookkeeping overlap.
+    struct Lane {
+        std::vector<FullJob *> jobs, enc_jobs, dev_jobs;
+        std::vector<State *> enc_states;
+        std::vector<int> enc_offsets;
+        std::vector<BatchRow> rows;
+        std::vector<SamplerRow> srows;
+        std::vector<Decoder *> sdecs;
+        bool pending = false;
+    };
+    int n_lanes = 1;
+    {
+        const char * e = getenv("WB200_LANES");
+        if (e && atoi(e) > 0) n_lanes = atoi(e);
+        else n_lanes = n_states / 64;  // measured on B200: lanes of >= 64 sequences keep the weight re-reads small
+        n_lanes = std::max(1, std::min(std::min(n_lanes, 4), std::min(n_states, step_max_lanes())));
+    }
+    std::vector<Lane> lanes((size_t) n_lanes);
+    for (int k = 0; k < n_states; ++k) lanes[(size_t) ((int64_t) k * n_lanes / n_states)].jobs.push_back(&jobs[(size_t) k]);
 
-    while (true) {
-        // ---- windows that need their encoder pass
-        enc_states.clear();
-        enc_offsets.clear();
-        enc_jobs.clear();
-        for (auto & j : jobs) {
-            if (j.phase != FullJob::WINDOW_BEGIN) continue;
-            if (j.window_begin()) {
-                enc_states.push_back(j.st);
-                enc_offsets.push_back(j.seek);
-                enc_jobs.push_back(&j);
+    auto encode_jobs = [&](Lane & ln, const std::vector<Lane *> & from) {
+        ln.enc_states.clear();
+        ln.enc_offsets.clear();
+        ln.enc_jobs.clear();
+        for (Lane * src : from)
+            for (FullJob * j : src->jobs) {
+                if (j->phase != FullJob::WINDOW_BEGIN) continue;
+                if (j->window_begin()) {
+                    ln.enc_states.push_back(j->st);
+                    ln.enc_offsets.push_back(j->seek);
+                    ln.enc_jobs.push_back(j);
+                }
             }
+        if (ln.enc_jobs.empty()) return;
+        if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
+            log_error("%s: failed to encode\n", __func__);
+            for (auto * j : ln.enc_jobs) j->finish(-6);
+        } else {
+            for (auto * j : ln.enc_jobs) j->after_encode();
         }
-        if (!enc_jobs.empty()) {
-            if (!stage_encode(*ctx, enc_states.data(), enc_offsets.data(), (int) enc_jobs.size())) {
-                log_error("%s: failed to encode\n", __func__);
-                for (auto * j : enc_jobs) j->finish(-6);
+    };
+    // the first windows of every lane go through the encoder as one batch
+    {
+        std::vector<Lane *> all;
+        for (auto & ln : lanes) all.push_back(&ln);
+        encode_jobs(lanes[0], all);
+    }
+
+    // advances a lane until it has a fused step in flight (pending) or nothing left to do
+    auto lane_advance = [&](Lane & ln, int lane_id) {
+        while (true) {
+            // ---- windows that need their encoder pass
+            encode_jobs(ln, {&ln});
+            // ---- gather the decoder rows of every live job
+            ln.rows.clear();
+            ln.srows.clear();
+            ln.sdecs.clear();
+            ln.dev_jobs.clear();
+            bool any_live = false, any_dists = false;
+            for (FullJob * jp : ln.jobs) {
+                FullJob & j = *jp;
+                if (j.phase == FullJob::DONE) continue;
+                any_live = true;
+                if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
+                if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
+                if (j.rows.empty()) continue;
+                // flagged rows of this job map to consecutive logits rows
+                int flagged = 0;
+                for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
+                const int base = (int) ln.srows.size();
+                if (flagged != (int) j.srows.size()) {
+                    log_error("%s: internal error: %d flagged rows vs %zu sampler rows\n", __func__, flagged, j.srows.size());
+                    j.finish(-9);
+                    continue;
+                }
+                ln.rows.insert(ln.rows.end(), j.rows.begin(), j.rows.end());
+                for (size_t q = 0; q < j.srows.size(); ++q) {
+                    SamplerRow sr = j.srows[q];
+                    sr.logits_row = base + (int) q;
+                    sr.work_slot = base + (int) q;
+                    ln.srows.push_back(sr);
+                    ln.sdecs.push_back(j.sdecs[q]);
+                    any_dists = any_dists || j.sdecs[q]->want_dists;
+                }
+                ln.dev_jobs.push_back(&j);
+            }
+            if (!any_live) return;
+            if (ln.dev_jobs.empty()) continue;
+
+            if (params_in.logits_filter_callback) {
+                // the callback sees host logits between the static suppressions and the timestamp rules (wc:6226-6228):
+                // not supported on the device sampler path
+                static bool warned = false;
+                if (!warned) log_msg(GGML_LOG_LEVEL_WARN, "%s: logits_filter_callback is ignored by the device sampler\n", __func__);
+                warned = true;
+            }
+            const int n_rows = (int) ln.rows.size();
+            const bool fused_step = step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
+            bool ok;
+            if (fused_step) {
+                // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
+                ok = stage_step_launch(*ctx, lane_id, n_lanes, ln.rows.data(), n_rows, sst, ln.srows.data());
+                if (ok) {
+                    ln.pending = true;
+                    return;
+                }
             } else {
-                for (auto * j : enc_jobs) j->after_encode();
+                ok = stage_decode(*ctx, ln.rows.data(), n_rows, false) &&
+                     stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data());
             }
-        }
-        // ---- gather the decoder rows of every live job
-        rows.clear();
-        srows.clear();
-        sdecs.clear();
-        dev_jobs.clear();
-        bool any_live = false, any_dists = false;
-        for (auto & j : jobs) {
-            if (j.phase == FullJob::DONE) continue;
-            any_live = true;
-            if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
-            if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
-            if (j.rows.empty()) continue;
-            // flagged rows of this job map to consecutive logits rows
-            int flagged = 0;
-            for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
-            const int base = (int) srows.size();
-            if (flagged != (int) j.srows.size()) {
-                log_error("%s: internal error: %d flagged rows vs %zu sampler rows\n", __func__, flagged, j.srows.size());
-                j.finish(-9);
+            if (!ok) {
+                log_error("%s: failed to decode\n", __func__);
+                for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
                 continue;
             }
-            rows.insert(rows.end(), j.rows.begin(), j.rows.end());
-            for (size_t q = 0; q < j.srows.size(); ++q) {
-                SamplerRow sr = j.srows[q];
-                sr.logits_row = base + (int) q;
-                sr.work_slot = base + (int) q;
-                srows.push_back(sr);
-                sdecs.push_back(j.sdecs[q]);
-                any_dists = any_dists || j.sdecs[q]->want_dists;
-            }
-            dev_jobs.push_back(&j);
+            for (auto * j : ln.dev_jobs) j->after_device();
         }
-        if (!any_live) break;
-        if (dev_jobs.empty()) continue;
-
-        bool ok;
-        const bool fused_step = step_eligible(*ctx, rows.data(), (int) rows.size(), any_dists) && rows.size() == srows.size();
-        if (fused_step) {
-            // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
-            ok = stage_step(*ctx, rows.data(), (int) rows.size(), sst, srows.data(), sdecs.data());
-        } else {
-            ok = stage_decode(*ctx, rows.data(), (int) rows.size(), false);
-        }
-        if (ok && params_in.logits_filter_callback) {
-            // the callback sees host logits between the static suppressions and the timestamp rules (wc:6226-6228):
-            // not supported on the device sampler path
-            static bool warned = false;
-            if (!warned) log_msg(GGML_LOG_LEVEL_WARN, "%s: logits_filter_callback is ignored by the device sampler\n", __func__);
-            warned = true;
-        }
-        if (!fused_step) ok = ok && stage_sample(*ctx, sst, srows.data(), (int) srows.size(), any_dists, sdecs.data());
-        if (!ok) {
+    };
+    auto lane_complete = [&](Lane & ln, int lane_id) {
+        ln.pending = false;
+        if (!stage_step_wait(*ctx, lane_id, ln.rows.data(), (int) ln.rows.size(), ln.sdecs.data())) {
             log_error("%s: failed to decode\n", __func__);
-            for (auto * j : dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
-            continue;
+            for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
+            return;
         }
-        for (auto * j : dev_jobs) j->after_device();
+        for (auto * j : ln.dev_jobs) j->after_device();
+    };
+
+    if (n_lanes > 1) cudaStreamSynchronize(ctx->stream);  // lanes > 0 run on their own streams: everything queued so far is done
+    for (int l = 0; l < n_lanes; ++l) lane_advance(lanes[(size_t) l], l);
+    while (true) {
+        bool any_pending = false;
+        for (int l = 0; l < n_lanes; ++l) {
+            Lane & ln = lanes[(size_t) l];
+            if (!ln.pending) continue;
+            any_pending = true;
+            lane_complete(ln, l);
+            lane_advance(ln, l);
+        }
+        if (!any_pending) break;
     }
     int ret = 0;
     for (auto & j : jobs)

@@ -369,6 +369,18 @@ gemm_wcluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
 // ---- host side: plan (split / stages) and launch --------------------------------------------------------------
 static std::atomic<uint64_t> g_step_launches{0};
 static bool g_pdl = true;  // launch with programmatic stream serialization (WB200_NO_PDL=1 switches it off)
+static int env_int(const char * name, int dflt) {
+    const char * e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+static int g_launch_prio = 0;  // cudaLaunchAttributePriority of the next launches (0: none; set around issue_step when lanes run)
+
+// Tuning of the kernels that share the SMs when several decode lanes are in flight (set by stage_step_launch):
+// CTAs per SM and ring depth of the persistent cross attention, shared-memory cap of the cluster GEMM.
+struct LaneTuning {
+    int xs_ctas_per_sm = 2, xs_stages = 5, wc_smem_cap = 192 * 1024;
+};
+static LaneTuning g_tune;
 
 struct WsPlan {
     int tiles, split, kb_total, kb_per_split, stages, n_pad, smem;
@@ -405,11 +417,20 @@ static bool launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (pdl && g_pdl) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (g_launch_prio != 0) {  // lanes: the bandwidth-bound cross attention yields SM slots to the other lanes' short kernels
+        at[na].id = cudaLaunchAttributePriority;
+        at[na].val.priority = g_launch_prio;
+        ++na;
+    }
     cfg.attrs = at;
-    cfg.numAttrs = (pdl && g_pdl) ? 1 : 0;
+    cfg.numAttrs = na;
     WB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
     g_step_launches.fetch_add(1);
     return true;
@@ -468,7 +489,7 @@ static WcPlan wc_plan(int n, int N_out, int K) {
     p.split        = ceil_div(p.kb_total, p.kb_per_split);
     p.tok_per_rank = ceil_div(n, p.split);
     const int stage_bytes = WS_A_BYTES + p.n_pad * 128;
-    p.stages = std::max(1, std::min(std::min(4, p.kb_per_split), (192 * 1024) / stage_bytes));
+    p.stages = std::max(1, std::min(std::min(4, p.kb_per_split), g_tune.wc_smem_cap / stage_bytes));
     p.smem   = std::max(p.stages * stage_bytes, p.n_pad * 512) + 1024 + 256;
     uint32_t c = 32;
     while ((int) c < p.n_pad) c <<= 1;
@@ -508,13 +529,23 @@ static bool gemm_wcluster(const __half * W, const __half * X, int n, int N_out, 
     cfg.blockDim = dim3(WS_THREADS);
     cfg.dynamicSmemBytes = (size_t) p.smem;
     cfg.stream = s;
-    cudaLaunchAttribute at[2];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = p.split; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute at[3];
+    int na = 0;
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = p.split; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+    ++na;
+    if (pdl && g_pdl) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (g_launch_prio != 0) {
+        at[na].id = cudaLaunchAttributePriority;
+        at[na].val.priority = g_launch_prio;
+        ++na;
+    }
     cfg.attrs = at;
-    cfg.numAttrs = (pdl && g_pdl) ? 2 : 1;
+    cfg.numAttrs = na;
     WB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_wcluster_kernel, tw, tx, a));
     g_step_launches.fetch_add(1);
     return true;
@@ -779,8 +810,11 @@ gelu_reduce_kernel(GeluArgs a) {
 // =============================================================================================
 // cross_attn_step: the kernel that bounds batched decoding (2 * T * 64 * 2 B of K/V per row, head and layer)
 // =============================================================================================
-// grid (H, n).  8 consumer warps + 1 producer warp.  The producer streams the contiguous K panel [T][64] f16 and then
-// the V panel of this (state, layer, head) in 16 KB chunks (128 keys) with cp.async.bulk into an mbarrier ring
+// Persistent: a fixed number of CTAs (a multiple of the SM count, so that the kernel's shared-memory footprint per SM is
+// known and the other decode lanes' kernels can co-reside) walk the H*n (row, head) items in a strided order; the ring
+// keeps running across items, so the producer already streams the next item's K panel while the consumers finish the
+// softmax / P.V / output of the current one.  8 consumer warps + 1 producer warp.  The producer streams the contiguous K
+// panel [T][64] f16 and then the V panel of a (state, layer, head) in 16 KB chunks (128 keys) with cp.async.bulk into an mbarrier ring
 // (L2 evict-first: every byte is used once per step); consumers compute scores from shared memory, the
 // row softmax (max, exp, double sum, 1/sum: ggml_soft_max_ext, ops.cpp:4731-4827; scale applied to K.Q as wc:2732-2734),
 // round P to f16 (mul_mat src1 conversion) and accumulate P.V in f32.  Q is finished from the cross-Q split-K partials.
@@ -795,6 +829,7 @@ struct CrossArgs {
     float scale;
     __half * out;           // [n][S]
     int stages;
+    int items;              // H * n (row, head) pairs, walked by a fixed number of persistent CTAs
 };
 
 static constexpr int XS_CONSUMERS  = 256;
@@ -815,7 +850,7 @@ cross_attn_step_kernel(CrossArgs a) {
     __shared__ double s_redd[8];
     __shared__ float s_acc[8][4][64];
 
-    const int h = blockIdx.x, j = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int T = a.T, S = a.S;
     const int nck = (T + XS_CHUNK_ROWS - 1) / XS_CHUNK_ROWS;  // chunks per panel
     if (tid == 0) {
@@ -826,28 +861,30 @@ cross_attn_step_kernel(CrossArgs a) {
         mbar_fence_init();
     }
     __syncthreads();
-    pdl_launch_dependents();
     pdl_wait();
-    const CrossKvRow r = a.rows[j];
 
     if (warp == 8) {
         // ---------------- producer ----------------
         if (lane == 0) {
             const uint64_t pol = l2_policy_evict_first();
-            const __half * kp = r.kv_base + ((int64_t) a.layer * 2 * a.H + h) * (int64_t) T * 64;
-            const __half * vp = r.kv_base + ((int64_t) a.layer * 2 * a.H + a.H + h) * (int64_t) T * 64;
             int stage = 0;
             uint32_t phase = 0;
-            for (int c = 0; c < 2 * nck; ++c) {
-                const int ci = c < nck ? c : c - nck;
-                const int rows = min(XS_CHUNK_ROWS, T - ci * XS_CHUNK_ROWS);
-                const __half * src = (c < nck ? kp : vp) + (int64_t) ci * XS_CHUNK_ROWS * 64;
-                mbar_wait(empty + stage, phase ^ 1);
-                mbar_expect_tx(full + stage, (uint32_t) rows * 128);
-                bulk_load_1d_hint(ring + stage * XS_CHUNK_BYTES, src, (uint32_t) rows * 128, full + stage, pol);
-                if (++stage == a.stages) {
-                    stage = 0;
-                    phase ^= 1;
+            for (int w = blockIdx.x; w < a.items; w += gridDim.x) {
+                const int h = w % a.H, j = w / a.H;
+                const __half * kv_base = a.rows[j].kv_base;
+                const __half * kp = kv_base + ((int64_t) a.layer * 2 * a.H + h) * (int64_t) T * 64;
+                const __half * vp = kv_base + ((int64_t) a.layer * 2 * a.H + a.H + h) * (int64_t) T * 64;
+                for (int c = 0; c < 2 * nck; ++c) {
+                    const int ci = c < nck ? c : c - nck;
+                    const int rows = min(XS_CHUNK_ROWS, T - ci * XS_CHUNK_ROWS);
+                    const __half * src = (c < nck ? kp : vp) + (int64_t) ci * XS_CHUNK_ROWS * 64;
+                    mbar_wait(empty + stage, phase ^ 1);
+                    mbar_expect_tx(full + stage, (uint32_t) rows * 128);
+                    bulk_load_1d_hint(ring + stage * XS_CHUNK_BYTES, src, (uint32_t) rows * 128, full + stage, pol);
+                    if (++stage == a.stages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
             }
         }
@@ -855,128 +892,155 @@ cross_attn_step_kernel(CrossArgs a) {
     }
 
     // ---------------- consumers (warps 0..7) ----------------
-    if (tid < 64) {
-        float qv;
-        if (a.q_f16 != nullptr) {
-            qv = __half2float(a.q_f16[(int64_t) j * S + h * 64 + tid]);
-        } else {
-            const float * p = a.partial + (int64_t) j * S + h * 64 + tid;
-            float acc = p[0];
-            for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
-            acc = __fadd_rn(acc, __ldg(a.bias + h * 64 + tid));
-            qv = __half2float(__float2half_rn(acc));
-        }
-        s_q[tid] = qv;
-    }
-    named_bar_sync(1, XS_CONSUMERS);
-
     const int sub = lane & 7, kq = lane >> 3;
-    float qf[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) qf[e] = s_q[sub * 8 + e];
-
     int stage = 0;
     uint32_t phase = 0;
-    float mx = -INFINITY;
-    for (int c = 0; c < nck; ++c) {
-        const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
-        mbar_wait(full + stage, phase);
-        const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
-#pragma unroll
-        for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
-            const int rr = it * 32 + warp * 4 + kq;
-            float acc = 0.0f;
-            if (rr < rows) {
-                const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
-                const __half2 * hp = (const __half2 *) &u;
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float2 f = __half22float2(hp[e]);
-                    acc = fmaf(f.x, qf[e * 2], acc);
-                    acc = fmaf(f.y, qf[e * 2 + 1], acc);
-                }
+    for (int w = blockIdx.x; w < a.items; w += gridDim.x) {
+        const int h = w % a.H, j = w / a.H;
+        // the dependent kernel's CTAs hold shared memory while they wait: let them in only near the end of this one
+        if (w + (int) gridDim.x >= a.items) pdl_launch_dependents();
+        if (tid < 64) {
+            float qv;
+            if (a.q_f16 != nullptr) {
+                qv = __half2float(a.q_f16[(int64_t) j * S + h * 64 + tid]);
+            } else {
+                const float * p = a.partial + (int64_t) j * S + h * 64 + tid;
+                float acc = p[0];
+                for (int s = 1; s < a.split; ++s) acc = __fadd_rn(acc, p[(int64_t) s * a.split_stride]);
+                acc = __fadd_rn(acc, __ldg(a.bias + h * 64 + tid));
+                qv = __half2float(__float2half_rn(acc));
             }
-            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-            if (rr < rows && sub == 0) {
-                const float sc = __fmul_rn(acc, a.scale);
-                s_sc[c * XS_CHUNK_ROWS + rr] = sc;
-                mx = fmaxf(mx, sc);
-            }
+            s_q[tid] = qv;
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty + stage);
-        if (++stage == a.stages) {
-            stage = 0;
-            phase ^= 1;
-        }
-    }
-    mx = warp_max(mx);
-    if (lane == 0) s_red[warp] = mx;
-    named_bar_sync(1, XS_CONSUMERS);
-    mx = s_red[0];
-#pragma unroll
-    for (int w = 1; w < 8; ++w) mx = fmaxf(mx, s_red[w]);
-    double sum = 0.0;
-    for (int t = tid; t < T; t += XS_CONSUMERS) {
-        const float e = expf(__fsub_rn(s_sc[t], mx));
-        s_sc[t] = e;
-        sum += (double) e;
-    }
-    sum = warp_sum_d(sum);
-    if (lane == 0) s_redd[warp] = sum;
-    named_bar_sync(1, XS_CONSUMERS);
-    sum = 0.0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) sum += s_redd[w];
-    const float inv = (float) (1.0 / sum);
-    for (int t = tid; t < T; t += XS_CONSUMERS) s_sc[t] = __half2float(__float2half_rn(__fmul_rn(s_sc[t], inv)));
-    named_bar_sync(1, XS_CONSUMERS);
+        named_bar_sync(1, XS_CONSUMERS);
 
-    float acc[8];
+        float qf[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
-    for (int c = 0; c < nck; ++c) {
-        const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
-        mbar_wait(full + stage, phase);
-        const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
+        for (int e = 0; e < 8; ++e) qf[e] = s_q[sub * 8 + e];
+
+        float mx = -INFINITY;
+        for (int c = 0; c < nck; ++c) {
+            const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
+            mbar_wait(full + stage, phase);
+            const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
 #pragma unroll
-        for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
-            const int rr = it * 32 + warp * 4 + kq;
-            if (rr < rows) {
-                const float p = s_sc[c * XS_CHUNK_ROWS + rr];
-                const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
-                const __half2 * hp = (const __half2 *) &u;
+            for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
+                const int rr = it * 32 + warp * 4 + kq;
+                float acc = 0.0f;
+                if (rr < rows) {
+                    const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
+                    const __half2 * hp = (const __half2 *) &u;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float2 f = __half22float2(hp[e]);
-                    acc[e * 2]     = fmaf(p, f.x, acc[e * 2]);
-                    acc[e * 2 + 1] = fmaf(p, f.y, acc[e * 2 + 1]);
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 f = __half22float2(hp[e]);
+                        acc = fmaf(f.x, qf[e * 2], acc);
+                        acc = fmaf(f.y, qf[e * 2 + 1], acc);
+                    }
+                }
+                acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+                if (rr < rows && sub == 0) {
+                    const float sc = __fmul_rn(acc, a.scale);
+                    s_sc[c * XS_CHUNK_ROWS + rr] = sc;
+                    mx = fmaxf(mx, sc);
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + stage);
+            if (++stage == a.stages) {
+                stage = 0;
+                phase ^= 1;
+            }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty + stage);
-        if (++stage == a.stages) {
-            stage = 0;
-            phase ^= 1;
+        mx = warp_max(mx);
+        if (lane == 0) s_red[warp] = mx;
+        named_bar_sync(1, XS_CONSUMERS);
+        mx = s_red[0];
+#pragma unroll
+        for (int w8 = 1; w8 < 8; ++w8) mx = fmaxf(mx, s_red[w8]);
+        double sum = 0.0;
+        for (int t = tid; t < T; t += XS_CONSUMERS) {
+            const float e = expf(__fsub_rn(s_sc[t], mx));
+            s_sc[t] = e;
+            sum += (double) e;
         }
-    }
+        sum = warp_sum_d(sum);
+        if (lane == 0) s_redd[warp] = sum;
+        named_bar_sync(1, XS_CONSUMERS);
+        sum = 0.0;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) s_acc[warp][kq][sub * 8 + e] = acc[e];
-    named_bar_sync(1, XS_CONSUMERS);
-    if (tid < 64) {
-        float o = 0.0f;
+        for (int w8 = 0; w8 < 8; ++w8) sum += s_redd[w8];
+        const float inv = (float) (1.0 / sum);
+        for (int t = tid; t < T; t += XS_CONSUMERS) s_sc[t] = __half2float(__float2half_rn(__fmul_rn(s_sc[t], inv)));
+        named_bar_sync(1, XS_CONSUMERS);
+
+        float acc[8];
 #pragma unroll
-        for (int w = 0; w < 8; ++w)
+        for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
+        for (int c = 0; c < nck; ++c) {
+            const int rows = min(XS_CHUNK_ROWS, T - c * XS_CHUNK_ROWS);
+            mbar_wait(full + stage, phase);
+            const uint8_t * buf = ring + stage * XS_CHUNK_BYTES;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) o += s_acc[w][g][tid];
-        a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
+            for (int it = 0; it < XS_CHUNK_ROWS / 32; ++it) {
+                const int rr = it * 32 + warp * 4 + kq;
+                if (rr < rows) {
+                    const float p = s_sc[c * XS_CHUNK_ROWS + rr];
+                    const uint4 u = *(const uint4 *) (buf + rr * 128 + sub * 16);
+                    const __half2 * hp = (const __half2 *) &u;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 f = __half22float2(hp[e]);
+                        acc[e * 2]     = fmaf(p, f.x, acc[e * 2]);
+                        acc[e * 2 + 1] = fmaf(p, f.y, acc[e * 2 + 1]);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + stage);
+            if (++stage == a.stages) {
+                stage = 0;
+                phase ^= 1;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s_acc[warp][kq][sub * 8 + e] = acc[e];
+        named_bar_sync(1, XS_CONSUMERS);
+        if (tid < 64) {
+            float o = 0.0f;
+#pragma unroll
+            for (int w8 = 0; w8 < 8; ++w8)
+#pragma unroll
+                for (int g = 0; g < 4; ++g) o += s_acc[w8][g][tid];
+            a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
+        }
     }
 }
 
 static int xs_smem_bytes(int T, int stages) { return stages * XS_CHUNK_BYTES + ((T + 31) & ~31) * 4 + 2 * stages * 8 + 128 + 64; }
+
+static int step_sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+static bool launch_cross(CrossArgs a, int n_rows, cudaStream_t s, bool pdl) {
+    static bool attr = false;
+    if (!attr) {
+        WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 132 * 1024));
+        attr = true;
+    }
+    a.items = a.H * n_rows;
+    a.stages = std::max(2, std::min(g_tune.xs_stages, 8));
+    const int grid = std::min(a.items, step_sm_count() * std::max(1, g_tune.xs_ctas_per_sm));
+    return launch_k(cross_attn_step_kernel, dim3(grid), dim3(XS_THREADS), (size_t) xs_smem_bytes(a.T, a.stages), s, pdl, a);
+}
 
 // =============================================================================================
 // the step graph
@@ -1044,12 +1108,12 @@ void free_ws(StepWs & ws) {
     ws = StepWs();
 }
 
-bool ensure_ws(Context & ctx, StepWs & ws, int n) {
+bool ensure_ws(Context & ctx, StepWs & ws, int n, cudaStream_t stream) {
     if (ws.base && ws.cap_n >= n) return true;
     const auto & hp = ctx.model.hp;
     const int S = hp.n_text_state, V = hp.n_vocab;
     const int cap = std::min(256, std::max(n, std::max(16, ws.cap_n * 2)));
-    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    WB_CUDA_OK(cudaStreamSynchronize(stream));
     free_ws(ws);  // graphs bake the workspace pointers
     size_t max_part = 0;
     const int shapes[4][2] = {{3 * S, S}, {S, S}, {S, 4 * S}, {4 * S, S}};
@@ -1093,9 +1157,7 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
     const SamplerRow * d_samp = (const SamplerRow *) (ws.d_stage + SL.o_samp);
     const float kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
     static bool attrs = false;
-    const int xs_stages = 5;
     if (!attrs) {
-        WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         WB_CUDA_OK(cudaFuncSetAttribute(self_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5120 * 4));
         attrs = true;
     }
@@ -1139,8 +1201,11 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
         {
             CrossArgs a{};
             a.q_f16 = ws.q16; a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
-            a.stages = xs_stages;
-            if (!launch_k(cross_attn_step_kernel, dim3(H, n), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, xs_stages), s, true, a)) return false;
+            const int prio = g_launch_prio;
+            g_launch_prio = 0;  // the bandwidth-bound kernel: other lanes' short kernels overtake its pending CTAs
+            const bool ok = launch_cross(a, n, s, true);
+            g_launch_prio = prio;
+            if (!ok) return false;
         }
         {
             WcOut o{};
@@ -1176,8 +1241,8 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
         {
             CrossArgs a{};
             a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * S; a.bias = l.cq.b; a.q_f16 = nullptr;
-            a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att; a.stages = xs_stages;
-            if (!launch_k(cross_attn_step_kernel, dim3(H, n), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, xs_stages), s, true, a)) return false;
+            a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
+            if (!launch_cross(a, n, s, true)) return false;
         }
         if (!gemm_wstream(l.co.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
         if (!ln(ws.partial, split, l.co.b, false, l.ln2)) return false;
@@ -1203,16 +1268,38 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
 
 }  // namespace
 
-static StepWs * step_ws(Context & ctx) {
-    if (!ctx.step) ctx.step = new StepWs();
-    return (StepWs *) ctx.step;
+// Decode lanes: independent groups of sequences, each with its own stream, workspace and step graphs.  While one
+// lane's cross attention saturates HBM, the latency-bound kernels of the other lanes (and the host's token bookkeeping
+// for a finished lane) run underneath it.  Lane 0 shares the context's stream with the general stages.
+static constexpr int MAX_LANES = 8;
+struct StepLanes {
+    StepWs ws[MAX_LANES];
+    cudaStream_t stream[MAX_LANES] = {};
+    int64_t t0[MAX_LANES] = {};
+    int prio_hi = 0;
+};
+
+static StepLanes * step_lanes(Context & ctx) {
+    if (!ctx.step) {
+        StepLanes * L = new StepLanes();
+        int lo = 0, hi = 0;
+        if (getenv("WB200_NO_PRIO") == nullptr && cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess) L->prio_hi = hi;
+        ctx.step = L;
+    }
+    return (StepLanes *) ctx.step;
 }
+
+int step_max_lanes() { return MAX_LANES; }
 
 void step_release(Context & ctx) {
     if (!ctx.step) return;
-    StepWs * ws = (StepWs *) ctx.step;
-    free_ws(*ws);
-    delete ws;
+    StepLanes * L = (StepLanes *) ctx.step;
+    for (int i = 0; i < MAX_LANES; ++i) {
+        if (L->stream[i]) cudaStreamSynchronize(L->stream[i]);
+        free_ws(L->ws[i]);
+        if (i > 0 && L->stream[i]) cudaStreamDestroy(L->stream[i]);
+    }
+    delete L;
     ctx.step = nullptr;
 }
 
@@ -1242,13 +1329,20 @@ bool step_eligible(const Context & ctx, const BatchRow * rows, int n, bool any_h
     return true;
 }
 
-bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows, Decoder ** decs) {
+bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows) {
     WB_CUDA_OK(cudaSetDevice(ctx.model.device));
-    const int64_t t0 = time_us();
+    WB_CHECK(lane >= 0 && lane < MAX_LANES, "decode lane %d out of range\n", lane);
     static const bool no_graph = getenv("WB200_STEP_NO_GRAPH") != nullptr;
     g_pdl = getenv("WB200_NO_PDL") == nullptr;
-    StepWs & ws = *step_ws(ctx);
-    if (!ensure_ws(ctx, ws, n)) return false;
+    StepLanes & L = *step_lanes(ctx);
+    if (!L.stream[lane]) {
+        if (lane == 0) L.stream[0] = ctx.stream;
+        else WB_CUDA_OK(cudaStreamCreateWithFlags(&L.stream[lane], cudaStreamNonBlocking));
+    }
+    cudaStream_t s = L.stream[lane];
+    L.t0[lane] = time_us();
+    StepWs & ws = L.ws[lane];
+    if (!ensure_ws(ctx, ws, n, s)) return false;
     const int T = rows[0].st->cross_T;
     const StageLayout SL = stage_layout(n);
     int * h_tok = (int *) (ws.h_stage + SL.o_tok);
@@ -1274,11 +1368,23 @@ bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic
         h_samp[i].logits_row = i;
         h_samp[i].work_slot = i;
     }
-    cudaStream_t s = ctx.stream;
+    // Several lanes in flight: every kernel's footprint per SM is bounded so that a lane's short kernels always find room
+    // next to another lane's cross attention (one persistent CTA per SM, ~97 KB) -- DESIGN.md 4.3.
+    const bool multi = n_lanes > 1;
+    LaneTuning tune;
+    tune.xs_ctas_per_sm = env_int("WB200_XS_CPS", multi ? 1 : 2);
+    tune.xs_stages = env_int("WB200_XS_STAGES", 5);
+    tune.wc_smem_cap = env_int("WB200_WC_SMEM_KB", multi ? 100 : 192) * 1024;
+    g_tune = tune;
+    g_launch_prio = multi ? L.prio_hi : 0;
     if (no_graph) {
-        if (!issue_step(ctx, ws, n, T, sst, s)) return false;
+        const bool ok = issue_step(ctx, ws, n, T, sst, s);
+        g_launch_prio = 0;
+        g_tune = LaneTuning();
+        if (!ok) return false;
     } else {
-        const uint64_t key = ((uint64_t) n << 32) | (uint32_t) T;
+        const uint64_t key = ((uint64_t) n << 40) | ((uint64_t) (tune.xs_ctas_per_sm & 15) << 36) | ((uint64_t) (tune.xs_stages & 15) << 32) |
+                             ((uint64_t) ((tune.wc_smem_cap >> 12) & 255) << 24) | ((uint64_t) multi << 23) | (uint32_t) (T & 0x7fffff);
         auto it = ws.graphs.find(key);
         if (it == ws.graphs.end()) {
             const uint64_t l0 = g_step_launches.load() + kernel_launch_count();
@@ -1288,6 +1394,7 @@ bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic
             const bool ok = issue_step(ctx, ws, n, T, sst, s);
             const cudaError_t e = cudaStreamEndCapture(s, &graph);
             prof_suspend(false);
+            g_launch_prio = 0;
             if (!ok || e != cudaSuccess || graph == nullptr) {
                 if (graph) cudaGraphDestroy(graph);
                 log_error("%s: capturing the decode-step graph failed (%s)\n", __func__, cudaGetErrorString(e));
@@ -1305,18 +1412,31 @@ bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic
             g_step_launches.fetch_sub(ge.launches - 1);
             it = ws.graphs.emplace(key, ge).first;
         }
+        g_launch_prio = 0;
+        g_tune = LaneTuning();
         WB_CUDA_OK(cudaGraphLaunch(it->second.exec, s));
         g_step_launches.fetch_add(it->second.launches);
     }
-    WB_CUDA_OK(cudaStreamSynchronize(s));
+    return true;
+}
+
+bool stage_step_wait(Context & ctx, int lane, const BatchRow * rows, int n, Decoder ** decs) {
+    StepLanes & L = *step_lanes(ctx);
+    WB_CHECK(lane >= 0 && lane < MAX_LANES && L.stream[lane], "decode lane %d was never launched\n", lane);
+    WB_CUDA_OK(cudaStreamSynchronize(L.stream[lane]));
+    const StepWs & ws = L.ws[lane];
     for (int i = 0; i < n; ++i)
         if (decs && decs[i]) decs[i]->picked = ws.h_out[i];
-    const int64_t dt = time_us() - t0;
+    const int64_t dt = time_us() - L.t0[lane];
     for (int i = 0; i < n; ++i) {  // wc:2982-2991: single-token decodes
         rows[i].st->t_decode_us += dt / n;
         rows[i].st->n_decode++;
     }
     return true;
+}
+
+bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows, Decoder ** decs) {
+    return stage_step_launch(ctx, 0, 1, rows, n, sst, srows) && stage_step_wait(ctx, 0, rows, n, decs);
 }
 
 uint64_t step_launch_count() { return g_step_launches.load(); }
@@ -1361,14 +1481,13 @@ bool test_gemm_wstream(const __half * w, const __half * x, float * out, int n, i
 }
 
 static bool launch_cross_test(const __half * q, const CrossKvRow * d_rows, __half * out, int n_rows, int H, int T, int layer, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) {
-        WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        attr = true;
-    }
     CrossArgs a{};
-    a.q_f16 = q; a.rows = d_rows; a.H = H; a.T = T; a.S = H * 64; a.layer = layer; a.scale = (float) pow(64.0, -0.25); a.out = out; a.stages = 5;
-    return launch_k(cross_attn_step_kernel, dim3(H, n_rows), dim3(XS_THREADS), (size_t) xs_smem_bytes(T, 5), s, false, a);
+    a.q_f16 = q; a.rows = d_rows; a.H = H; a.T = T; a.S = H * 64; a.layer = layer; a.scale = (float) pow(64.0, -0.25); a.out = out;
+    g_tune.xs_ctas_per_sm = env_int("WB200_XS_CPS", 2);
+    g_tune.xs_stages = env_int("WB200_XS_STAGES", 5);
+    const bool ok = launch_cross(a, n_rows, s, false);
+    g_tune = LaneTuning();
+    return ok;
 }
 
 bool test_cross_attn_step(const __half * q_f16, const __half * kv, __half * out, int n_rows, int H, int T) {

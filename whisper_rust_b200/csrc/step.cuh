@@ -23,6 +23,11 @@ namespace wb {
 bool step_eligible(const Context & ctx, const BatchRow * rows, int n, bool any_host_dists);
 // decoder forward + sampler for one token per row; results land in decs[i]->picked.
 bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows, Decoder ** decs);
+// the same, split for decode lanes: launch on lane `lane`'s stream without waiting / wait for it and collect the picks.
+// Lanes hold disjoint sets of states; a lane must be waited for before its next launch.
+bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows);
+bool stage_step_wait(Context & ctx, int lane, const BatchRow * rows, int n, Decoder ** decs);
+int step_max_lanes();
 void step_release(Context & ctx);
 uint64_t step_launch_count();
 
