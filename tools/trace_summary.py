@@ -1,0 +1,19 @@
+#!/usr/bin/env python
+"""Summarise WB200_STEP_TRACE dumps: per lane, time per kernel kind inside the concurrent run and the lanes' overlap."""
+import json, sys
+from collections import defaultdict
+for line in open(sys.argv[1]):
+    d = json.loads(line)
+    t0 = min(min(l["t_ns"]) for l in d["lanes"])
+    for l in d["lanes"]:
+        t, names = l["t_ns"], l["names"]
+        dur = defaultdict(float); cnt = defaultdict(int)
+        for i in range(len(t) - 1):
+            dur[names[i]] += (t[i + 1] - t[i]) / 1e3; cnt[names[i]] += 1
+        tot = (t[-1] - t[0]) / 1e3
+        print(f"lane {l['lane']} n={l['n']} start={(t[0]-t0)/1e3:9.1f}us span={tot:9.1f}us  " +
+              "  ".join(f"{k}:{dur[k]/cnt[k]:.1f}x{cnt[k]}" for k in sorted(dur)))
+    if len(sys.argv) > 2:
+        l = d["lanes"][0]
+        for i in range(int(sys.argv[2])):
+            print(l["names"][i], (l["t_ns"][i] - t0) / 1e3)

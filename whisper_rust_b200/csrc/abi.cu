@@ -959,6 +959,10 @@ int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c
     if (strcmp(kind, "cross_attn_step") == 0) ok = bench_cross_attn_step(n_rows, a /*H*/, b /*T*/, c /*layers*/, iters, &r);
     else if (strcmp(kind, "gemm_wstream") == 0) ok = bench_gemm_wstream(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
     else if (strcmp(kind, "gemm_wcluster") == 0) ok = bench_gemm_wcluster(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
+    else if (strcmp(kind, "overlap_gemm") == 0) {
+        ok = bench_overlap_gemm(n_rows, a /*N_out*/, b /*K*/, c /*n_weights*/, iters, &r);
+        if (ok && us_per_launch) us_per_launch[1] = 1e-3 * r.launches;  // background cross-attention us per launch
+    }
     if (!ok) return 1;
     if (us_per_launch) *us_per_launch = r.us_per_launch;
     if (bytes_per_launch) *bytes_per_launch = r.bytes_per_launch;

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <thread>
 #include <map>
 #include <regex>
 
@@ -931,8 +932,8 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     {
         const char * e = getenv("WB200_LANES");
         if (e && atoi(e) > 0) n_lanes = atoi(e);
-        else n_lanes = n_states / 64;  // measured on B200: lanes of >= 64 sequences keep the weight re-reads small
-        n_lanes = std::max(1, std::min(std::min(n_lanes, 4), std::min(n_states, step_max_lanes())));
+        else n_lanes = n_states >= 128 ? 2 : 1;  // measured on B200
+        n_lanes = std::max(1, std::min(n_lanes, std::min(n_states, step_max_lanes())));
     }
     std::vector<Lane> lanes((size_t) n_lanes);
     for (int k = 0; k < n_states; ++k) lanes[(size_t) ((int64_t) k * n_lanes / n_states)].jobs.push_back(&jobs[(size_t) k]);
@@ -1047,15 +1048,27 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
 
     if (n_lanes > 1) cudaStreamSynchronize(ctx->stream);  // lanes > 0 run on their own streams: everything queued so far is done
     for (int l = 0; l < n_lanes; ++l) lane_advance(lanes[(size_t) l], l);
+    int trace_round = getenv("WB200_STEP_TRACE") ? 0 : -1;
     while (true) {
-        bool any_pending = false;
+        if (trace_round >= 0 && ++trace_round == 100) {
+            // in-situ timeline (step.cuh): drain every lane, dump the stamps of their last (concurrent) steps, resume
+            for (int l = 0; l < n_lanes; ++l)
+                if (lanes[(size_t) l].pending) lane_complete(lanes[(size_t) l], l);
+            step_trace_dump(*ctx);
+            for (int l = 0; l < n_lanes; ++l) lane_advance(lanes[(size_t) l], l);
+        }
+        // serve whichever lane finishes first (a fixed round-robin would hold every lane to the slowest one's pace)
+        bool any_pending = false, served = false;
         for (int l = 0; l < n_lanes; ++l) {
             Lane & ln = lanes[(size_t) l];
             if (!ln.pending) continue;
             any_pending = true;
+            if (n_lanes > 1 && !stage_step_ready(*ctx, l)) continue;
+            served = true;
             lane_complete(ln, l);
             lane_advance(ln, l);
         }
+        if (any_pending && !served) std::this_thread::yield();
         if (!any_pending) break;
     }
     int ret = 0;

@@ -26,8 +26,10 @@ bool stage_step(Context & ctx, const BatchRow * rows, int n, const SamplerStatic
 // the same, split for decode lanes: launch on lane `lane`'s stream without waiting / wait for it and collect the picks.
 // Lanes hold disjoint sets of states; a lane must be waited for before its next launch.
 bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows);
+bool stage_step_ready(Context & ctx, int lane);  // true once the lane's step has finished (non-blocking)
 bool stage_step_wait(Context & ctx, int lane, const BatchRow * rows, int n, Decoder ** decs);
 int step_max_lanes();
+void step_trace_dump(Context & ctx);  // WB200_STEP_TRACE=<file>: in-situ kernel timeline of the last step of every lane
 void step_release(Context & ctx);
 uint64_t step_launch_count();
 
@@ -45,6 +47,7 @@ bool test_gemm_wstream(const __half * w, const __half * x, float * out, int n, i
 bool test_gemm_wcluster(const __half * w, const __half * x, void * out, int n, int N_out, int K, const float * bias, int mode, float scale,
                         int scale_f1, const __half * gelu_table);
 bool bench_gemm_wcluster(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out);
+bool bench_overlap_gemm(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out);
 bool test_cross_attn_step(const __half * q_f16, const __half * kv, __half * out, int n_rows, int H, int T);
 
 }  // namespace wb
