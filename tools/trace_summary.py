@@ -5,7 +5,13 @@ from collections import defaultdict
 for line in open(sys.argv[1]):
     d = json.loads(line)
     t0 = min(min(l["t_ns"]) for l in d["lanes"])
-    for l in d["lanes"]:
+    lanes = []
+    for l in d["lanes"]:  # split paired steps into their two halves
+        subs = l.get("sub") or [0] * len(l["t_ns"])
+        for sub in sorted(set(subs)):
+            idx = [i for i, x in enumerate(subs) if x == sub]
+            lanes.append({"lane": f"{l['lane']}.{sub}", "n": l["n"], "t_ns": [l["t_ns"][i] for i in idx], "names": [l["names"][i] for i in idx]})
+    for l in lanes:
         t, names = l["t_ns"], l["names"]
         dur = defaultdict(float); cnt = defaultdict(int)
         for i in range(len(t) - 1):

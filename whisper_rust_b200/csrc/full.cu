@@ -932,7 +932,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     {
         const char * e = getenv("WB200_LANES");
         if (e && atoi(e) > 0) n_lanes = atoi(e);
-        else n_lanes = n_states >= 128 ? 2 : 1;  // measured on B200
+        else n_lanes = std::min(4, n_states / 64);  // measured on B200: 4 lanes of 64 rows beat 1 x 256 by ~5 %
         n_lanes = std::max(1, std::min(n_lanes, std::min(n_states, step_max_lanes())));
     }
     std::vector<Lane> lanes((size_t) n_lanes);
@@ -952,6 +952,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 }
             }
         if (ln.enc_jobs.empty()) return;
+        if (getenv("WB200_HOST_PROF")) fprintf(stderr, "host_prof: encode %zu windows\n", ln.enc_jobs.size());
         if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
             log_error("%s: failed to encode\n", __func__);
             for (auto * j : ln.enc_jobs) j->finish(-6);
@@ -966,9 +967,14 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         encode_jobs(lanes[0], all);
     }
 
+    // WB200_HOST_PROF=1: where the host time of the token loop goes (printed once per call)
+    const bool host_prof = getenv("WB200_HOST_PROF") != nullptr;
+    int64_t hp_gather = 0, hp_elig = 0, hp_launch = 0, hp_wait = 0, hp_after = 0, hp_steps = 0;
+    std::string hp_log;
     // advances a lane until it has a fused step in flight (pending) or nothing left to do
     auto lane_advance = [&](Lane & ln, int lane_id) {
         while (true) {
+            const int64_t tg0 = host_prof ? time_us() : 0;
             // ---- windows that need their encoder pass
             encode_jobs(ln, {&ln});
             // ---- gather the decoder rows of every live job
@@ -1015,11 +1021,16 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 warned = true;
             }
             const int n_rows = (int) ln.rows.size();
+            const int64_t tg1 = host_prof ? time_us() : 0;
             const bool fused_step = step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
+            const int64_t tg2 = host_prof ? time_us() : 0;
+            hp_gather += tg1 - tg0;
+            hp_elig += tg2 - tg1;
             bool ok;
             if (fused_step) {
                 // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
                 ok = stage_step_launch(*ctx, lane_id, n_lanes, ln.rows.data(), n_rows, sst, ln.srows.data());
+                if (host_prof) hp_launch += time_us() - tg2, ++hp_steps, hp_log += " " + std::to_string(n_rows);
                 if (ok) {
                     ln.pending = true;
                     return;
@@ -1038,12 +1049,15 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     };
     auto lane_complete = [&](Lane & ln, int lane_id) {
         ln.pending = false;
+        const int64_t tw0 = host_prof ? time_us() : 0;
         if (!stage_step_wait(*ctx, lane_id, ln.rows.data(), (int) ln.rows.size(), ln.sdecs.data())) {
             log_error("%s: failed to decode\n", __func__);
             for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
             return;
         }
+        const int64_t tw1 = host_prof ? time_us() : 0;
         for (auto * j : ln.dev_jobs) j->after_device();
+        if (host_prof) hp_wait += tw1 - tw0, hp_after += time_us() - tw1;
     };
 
     if (n_lanes > 1) cudaStreamSynchronize(ctx->stream);  // lanes > 0 run on their own streams: everything queued so far is done
@@ -1071,6 +1085,12 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         if (any_pending && !served) std::this_thread::yield();
         if (!any_pending) break;
     }
+    if (host_prof) fprintf(stderr, "host_prof: rows per step:%s\n", hp_log.c_str());
+    if (host_prof)
+        fprintf(stderr, "host_prof: %lld fused steps; us/step: gather %.1f eligible %.1f launch %.1f wait %.1f after_device %.1f\n", (long long) hp_steps,
+                hp_gather / (double) std::max<int64_t>(1, hp_steps), hp_elig / (double) std::max<int64_t>(1, hp_steps),
+                hp_launch / (double) std::max<int64_t>(1, hp_steps), hp_wait / (double) std::max<int64_t>(1, hp_steps),
+                hp_after / (double) std::max<int64_t>(1, hp_steps));
     int ret = 0;
     for (auto & j : jobs)
         if (j.ret != 0 && ret == 0) ret = j.ret;

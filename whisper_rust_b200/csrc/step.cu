@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <map>
 #include <vector>
@@ -392,9 +393,12 @@ static int g_launch_prio = 0;
 // timeline capture (WB200_STEP_TRACE): next free stamp slot and the label of every slot handed out
 static unsigned long long * g_trace_next = nullptr;
 static std::vector<const char *> * g_trace_names = nullptr;
+static std::vector<int> * g_trace_subs = nullptr;
+static int g_trace_sub = 0;  // which half of a paired step the next launches belong to
 static unsigned long long * trace_slot(const char * name) {
     if (!g_trace_next) return nullptr;
     if (g_trace_names) g_trace_names->push_back(name);
+    if (g_trace_subs) g_trace_subs->push_back(g_trace_sub);
     return g_trace_next++;
 }  // cudaLaunchAttributePriority of the next launches (0: none; set around issue_step when lanes run)
 
@@ -1101,9 +1105,10 @@ struct StepWs {
     size_t stage_bytes = 0;
     SamplerOut * h_out = nullptr;  // pinned
     SamplerOut * d_out = nullptr;
-    std::map<uint64_t, GraphEntry> graphs;
+    std::map<std::array<int, 8>, GraphEntry> graphs;
     unsigned long long * d_trace = nullptr;  // WB200_STEP_TRACE: one %globaltimer stamp per kernel of the step
     std::vector<const char *> trace_names;
+    std::vector<int> trace_subs;
     int trace_n = 0;                         // rows of the traced step
 };
 
@@ -1180,39 +1185,53 @@ bool ensure_ws(Context & ctx, StepWs & ws, int n, cudaStream_t stream) {
     return true;
 }
 
-// issues every launch of one decode step for n rows on `s` (live or under stream capture)
-bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & sst, cudaStream_t s) {
-    const Model & m = ctx.model;
-    const auto & hp = m.hp;
-    const int S = hp.n_text_state, H = hp.n_text_head, L = hp.n_text_layer, V = hp.n_vocab;
-    const StageLayout SL = stage_layout(n);
-    const int * d_tok = (const int *) (ws.d_stage + SL.o_tok);
-    const int * d_pos = (const int *) (ws.d_stage + SL.o_pos);
-    const SelfKvRow * d_self = (const SelfKvRow *) (ws.d_stage + SL.o_self);
-    const CrossKvRow * d_cross = (const CrossKvRow *) (ws.d_stage + SL.o_cross);
-    const SamplerRow * d_samp = (const SamplerRow *) (ws.d_stage + SL.o_samp);
-    const float kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
-    static bool attrs = false;
-    if (!attrs) {
-        WB_CUDA_OK(cudaFuncSetAttribute(self_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5120 * 4));
-        attrs = true;
-    }
-    WB_CHECK(S <= LN_THREADS * LN_MAX_PER_THREAD && (S % 64) == 0, "unsupported text state %d\n", S);
-    WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage, ws.h_stage, SL.bytes, cudaMemcpyHostToDevice, s));
+// The launches of one decode step for the n rows of one workspace, in the pieces the two issue orders below need.
+struct LaneIssue {
+    Context & ctx;
+    StepWs & ws;
+    int n, T;
+    cudaStream_t s;
+    const Model & m;
+    int S, H, L, V;
+    StageLayout SL;
+    const int *d_tok, *d_pos;
+    const SelfKvRow * d_self;
+    const CrossKvRow * d_cross;
+    const SamplerRow * d_samp;
+    float kq_scale;
 
-    auto ln = [&](const float * partial, int split, const float * bias, bool embed, const Norm & nm) {
+    LaneIssue(Context & c, StepWs & w, int n_, int T_, cudaStream_t s_)
+        : ctx(c), ws(w), n(n_), T(T_), s(s_), m(c.model), S(c.model.hp.n_text_state), H(c.model.hp.n_text_head), L(c.model.hp.n_text_layer),
+          V(c.model.hp.n_vocab), SL(stage_layout(n_)) {
+        d_tok = (const int *) (ws.d_stage + SL.o_tok);
+        d_pos = (const int *) (ws.d_stage + SL.o_pos);
+        d_self = (const SelfKvRow *) (ws.d_stage + SL.o_self);
+        d_cross = (const CrossKvRow *) (ws.d_stage + SL.o_cross);
+        d_samp = (const SamplerRow *) (ws.d_stage + SL.o_samp);
+        kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
+    }
+
+    bool ln(bool embed, const Norm & nm) {
         LnArgs a{};
-        a.partial = partial; a.split = split; a.split_stride = (int64_t) n * S; a.bias = bias;
         a.res = embed ? nullptr : ws.x;
         a.te = embed ? m.d_te : nullptr; a.pe = m.d_pe; a.tokens = d_tok; a.pos = d_pos;
-        a.x_out = ws.x; a.xa_out = ws.xa; a.gamma = nm.g; a.beta = nm.b; a.eps = hp.eps; a.S = S;
+        a.x_out = ws.x; a.xa_out = ws.xa; a.gamma = nm.g; a.beta = nm.b; a.eps = m.hp.eps; a.S = S;
         a.trace = trace_slot("ln");
         return launch_k(ln_reduce_kernel, dim3(n), dim3(LN_THREADS), 0, s, !embed, a);
-    };
-    if (!ln(nullptr, 0, nullptr, true, L > 0 ? m.dec[0].ln1 : m.d_ln)) return false;
-    // WB200_STEP=partials: the earlier design (split-K partials in global memory, reduced by the consumer kernels)
-    static const bool use_partials = [] { const char * e = getenv("WB200_STEP"); return e && strcmp(e, "partials") == 0; }();
-    for (int il = 0; il < L && !use_partials; ++il) {
+    }
+    // staging upload + token/position embedding + first LayerNorm
+    bool begin() {
+        static bool attrs = false;
+        if (!attrs) {
+            WB_CUDA_OK(cudaFuncSetAttribute(self_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5120 * 4));
+            attrs = true;
+        }
+        WB_CHECK(S <= LN_THREADS * LN_MAX_PER_THREAD && (S % 64) == 0, "unsupported text state %d\n", S);
+        WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage, ws.h_stage, SL.bytes, cudaMemcpyHostToDevice, s));
+        return ln(true, L > 0 ? m.dec[0].ln1 : m.d_ln);
+    }
+    // self-attention block and the cross-attention query of layer il (everything up to the K/V stream)
+    bool pre(int il) {
         const DecLayer & l = m.dec[il];
         {   // Q|K|V: bias, D^-1/4 on Q and K, f16 (wc:2558-2583)
             WcOut o{};
@@ -1230,27 +1249,33 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
             o.mode = WC_RESIDUAL; o.out = ws.x; o.ldo = S; o.bias = l.o.b;
             if (!gemm_wcluster(l.o.w, ws.att, n, S, S, o, s, true)) return false;
         }
-        if (!ln(nullptr, 0, nullptr, false, l.lnc)) return false;
+        if (!ln(false, l.lnc)) return false;
         {   // cross-attention query, f16 (wc:2700-2707)
             WcOut o{};
             o.mode = WC_F16; o.out = ws.q16; o.ldo = S; o.bias = l.cq.b;
             if (!gemm_wcluster(l.cq.w, ws.xa, n, S, S, o, s, true)) return false;
         }
-        {
-            CrossArgs a{};
-            a.q_f16 = ws.q16; a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
-            const int prio = g_launch_prio;
-            g_launch_prio = 0;  // the bandwidth-bound kernel: other lanes' short kernels overtake its pending CTAs
-            const bool ok = launch_cross(a, n, s, true);
-            g_launch_prio = prio;
-            if (!ok) return false;
-        }
+        return true;
+    }
+    // the HBM-bound kernel: streams this lane's cross K/V of layer il.  `pdl`: launch as a programmatic dependent
+    bool cross(int il, bool pdl) {
+        CrossArgs a{};
+        a.q_f16 = ws.q16; a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
+        const int prio = g_launch_prio;
+        g_launch_prio = 0;  // the bandwidth-bound kernel: the other lane's short kernels overtake its pending CTAs
+        const bool ok = launch_cross(a, n, s, pdl);
+        g_launch_prio = prio;
+        return ok;
+    }
+    // cross-attention output projection, MLP, and the LayerNorm that opens the next layer (or the final one)
+    bool post(int il) {
+        const DecLayer & l = m.dec[il];
         {
             WcOut o{};
             o.mode = WC_RESIDUAL; o.out = ws.x; o.ldo = S; o.bias = l.co.b;
             if (!gemm_wcluster(l.co.w, ws.att, n, S, S, o, s, true)) return false;
         }
-        if (!ln(nullptr, 0, nullptr, false, l.ln2)) return false;
+        if (!ln(false, l.ln2)) return false;
         {   // MLP: f16(gelu(W1.x + b1)) through the reference's f16 table, then x += W2.h + b2 (wc:2795-2814)
             WcOut o{};
             o.mode = WC_GELU; o.out = ws.hb; o.ldo = 4 * S; o.bias = l.fc1.b; o.gelu_table = m.gelu_table;
@@ -1259,48 +1284,67 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
             o2.mode = WC_RESIDUAL; o2.out = ws.x; o2.ldo = S; o2.bias = l.fc2.b;
             if (!gemm_wcluster(l.fc2.w, ws.hb, n, S, 4 * S, o2, s, true)) return false;
         }
-        if (!ln(nullptr, 0, nullptr, false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln)) return false;
+        return ln(false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln);
     }
-    for (int il = 0; il < L && use_partials; ++il) {
-        const DecLayer & l = m.dec[il];
-        int split = 1;
-        WsOut po{};
-        po.partial = ws.partial;
-        if (!gemm_wstream(l.qkv.w, ws.xa, n, 3 * S, S, po, 0, &split, s, true)) return false;
-        {
-            SelfArgs a{};
-            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * 3 * S; a.bias = l.qkv.b; a.scale = kq_scale;
-            a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
-            if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), (size_t) 5120 * 4, s, true, a)) return false;
-        }
-        if (!gemm_wstream(l.o.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
-        if (!ln(ws.partial, split, l.o.b, false, l.lnc)) return false;
-        if (!gemm_wstream(l.cq.w, ws.xa, n, S, S, po, 0, &split, s, true)) return false;
-        {
-            CrossArgs a{};
-            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * S; a.bias = l.cq.b; a.q_f16 = nullptr;
-            a.rows = d_cross; a.H = H; a.T = T; a.S = S; a.layer = il; a.scale = kq_scale; a.out = ws.att;
-            if (!launch_cross(a, n, s, true)) return false;
-        }
-        if (!gemm_wstream(l.co.w, ws.att, n, S, S, po, 0, &split, s, true)) return false;
-        if (!ln(ws.partial, split, l.co.b, false, l.ln2)) return false;
-        if (!gemm_wstream(l.fc1.w, ws.xa, n, 4 * S, S, po, 0, &split, s, true)) return false;
-        {
-            GeluArgs a{};
-            a.partial = ws.partial; a.split = split; a.split_stride = (int64_t) n * 4 * S; a.bias = l.fc1.b; a.gelu_table = m.gelu_table;
-            a.out = ws.hb; a.total = (int64_t) n * 4 * S; a.N = 4 * S;
-            if (!launch_k(gelu_reduce_kernel, dim3((unsigned) ceil_div64(a.total, 1024)), dim3(256), 0, s, true, a)) return false;
-        }
-        if (!gemm_wstream(l.fc2.w, ws.hb, n, S, 4 * S, po, 0, &split, s, true)) return false;
-        if (!ln(ws.partial, split, l.fc2.b, false, il + 1 < L ? m.dec[il + 1].ln1 : m.d_ln)) return false;
-    }
-    {   // tied-embedding logits (wc:2835)
+    // tied-embedding logits (wc:2835), sampler, picks to the host
+    bool finish(const SamplerStatic & sst) {
         WsOut d{};
         d.out = ws.logits; d.out_f16 = 0; d.ldo = V;
         if (!gemm_wstream(m.d_te, ws.xa, n, V, S, d, 1, nullptr, s, true)) return false;
+        if (!sample_rows(sst, ws.logits, V, d_samp, n, ws.samp_work, ws.d_out, s)) return false;
+        WB_CUDA_OK(cudaMemcpyAsync(ws.h_out, ws.d_out, (size_t) n * sizeof(SamplerOut), cudaMemcpyDeviceToHost, s));
+        return true;
     }
-    if (!sample_rows(sst, ws.logits, V, d_samp, n, ws.samp_work, ws.d_out, s)) return false;
-    WB_CUDA_OK(cudaMemcpyAsync(ws.h_out, ws.d_out, (size_t) n * sizeof(SamplerOut), cudaMemcpyDeviceToHost, s));
+};
+
+// issues every launch of one decode step for n rows on `s` (live or under stream capture)
+bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & sst, cudaStream_t s) {
+    LaneIssue a(ctx, ws, n, T, s);
+    if (!a.begin()) return false;
+    for (int il = 0; il < a.L; ++il)
+        if (!a.pre(il) || !a.cross(il, true) || !a.post(il)) return false;
+    return a.finish(sst);
+}
+
+// Interleaved issue: the rows are split into K groups that advance through the layers a fraction of a layer apart, as K
+// branches of ONE graph.  The HBM-bound cross attentions form a single chain A0 -> B0 -> C0 -> A1 -> B1 ... (full graph
+// edges through events), so exactly one K/V stream owns the memory system at a time while the other groups' latency-bound
+// kernels (GEMMs at a few rows, LayerNorm, self attention) run underneath it -- HBM never waits for them as long as a
+// group's short kernels fit under the other K-1 groups' K/V streams.
+bool issue_step_multi(Context & ctx, StepWs * const * w, const int * n, int K, int T, const SamplerStatic & sst, cudaStream_t * st,
+                      cudaEvent_t * ev /*[K * L + 2]*/) {
+    std::vector<LaneIssue> G;
+    G.reserve((size_t) K);
+    for (int k = 0; k < K; ++k) G.emplace_back(ctx, *w[k], n[k], T, st[k]);
+    static const bool cross_pdl = getenv("WB200_PAIR_PDL") != nullptr;
+    const int L = G[0].L;
+    cudaEvent_t fork = ev[K * L], join = ev[K * L + 1];
+    WB_CUDA_OK(cudaEventRecord(fork, st[0]));
+    for (int k = 1; k < K; ++k) WB_CUDA_OK(cudaStreamWaitEvent(st[k], fork, 0));
+    for (int k = 0; k < K; ++k) {
+        g_trace_sub = k;
+        if (!G[(size_t) k].begin()) return false;
+    }
+    for (int il = 0; il < L; ++il)
+        for (int k = 0; k < K; ++k) {
+            g_trace_sub = k;
+            LaneIssue & g = G[(size_t) k];
+            if (!g.pre(il)) return false;
+            const int link = il * K + k;  // position in the chain of K/V streams
+            if (link > 0) WB_CUDA_OK(cudaStreamWaitEvent(st[k], ev[link - 1], 0));  // the previous K/V stream has finished
+            if (!g.cross(il, link == 0 || cross_pdl)) return false;
+            WB_CUDA_OK(cudaEventRecord(ev[link], st[k]));
+            if (!g.post(il)) return false;
+        }
+    for (int k = 0; k < K; ++k) {
+        g_trace_sub = k;
+        if (!G[(size_t) k].finish(sst)) return false;
+    }
+    g_trace_sub = 0;
+    for (int k = 1; k < K; ++k) {
+        WB_CUDA_OK(cudaEventRecord(join, st[k]));
+        WB_CUDA_OK(cudaStreamWaitEvent(st[0], join, 0));
+    }
     return true;
 }
 
@@ -1310,10 +1354,16 @@ bool issue_step(Context & ctx, StepWs & ws, int n, int T, const SamplerStatic & 
 // lane's cross attention saturates HBM, the latency-bound kernels of the other lanes (and the host's token bookkeeping
 // for a finished lane) run underneath it.  Lane 0 shares the context's stream with the general stages.
 static constexpr int MAX_LANES = 8;
+static constexpr int MAX_GROUPS = 4;
 struct StepLanes {
     StepWs ws[MAX_LANES];
+    StepWs sub[MAX_LANES][MAX_GROUPS - 1];            // groups 1.. of an interleaved step (issue_step_multi)
     cudaStream_t stream[MAX_LANES] = {};
+    cudaStream_t sub_stream[MAX_LANES][MAX_GROUPS - 1] = {};  // capture-time branches of groups 1..
+    int groups[MAX_LANES] = {};                       // groups of the step in flight
+    int group_n[MAX_LANES][MAX_GROUPS] = {};          // and their row counts
     int64_t t0[MAX_LANES] = {};
+    std::vector<cudaEvent_t> events;      // fork/join and the cross-attention chain of the paired graph
     int prio_hi = 0;
 };
 
@@ -1345,6 +1395,8 @@ void step_trace_dump(Context & ctx) {
         if (cudaMemcpy(t.data(), ws.d_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) continue;
         fprintf(f, "%s{\"lane\": %d, \"n\": %d, \"names\": [", first ? "" : ", ", l, ws.trace_n);
         for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s\"%s\"", i ? "," : "", ws.trace_names[i]);
+        fprintf(f, "], \"sub\": [");
+        for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s%d", i ? "," : "", i < ws.trace_subs.size() ? ws.trace_subs[i] : 0);
         fprintf(f, "], \"t_ns\": [");
         for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s%llu", i ? "," : "", t[i]);
         fprintf(f, "]}");
@@ -1360,8 +1412,13 @@ void step_release(Context & ctx) {
     for (int i = 0; i < MAX_LANES; ++i) {
         if (L->stream[i]) cudaStreamSynchronize(L->stream[i]);
         free_ws(L->ws[i]);
+        for (int g = 0; g < MAX_GROUPS - 1; ++g) {
+            free_ws(L->sub[i][g]);
+            if (L->sub_stream[i][g]) cudaStreamDestroy(L->sub_stream[i][g]);
+        }
         if (i > 0 && L->stream[i]) cudaStreamDestroy(L->stream[i]);
     }
+    for (cudaEvent_t e : L->events) cudaEventDestroy(e);
     delete L;
     ctx.step = nullptr;
 }
@@ -1392,21 +1449,8 @@ bool step_eligible(const Context & ctx, const BatchRow * rows, int n, bool any_h
     return true;
 }
 
-bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows) {
-    WB_CUDA_OK(cudaSetDevice(ctx.model.device));
-    WB_CHECK(lane >= 0 && lane < MAX_LANES, "decode lane %d out of range\n", lane);
-    static const bool no_graph = getenv("WB200_STEP_NO_GRAPH") != nullptr;
-    g_pdl = getenv("WB200_NO_PDL") == nullptr;
-    StepLanes & L = *step_lanes(ctx);
-    if (!L.stream[lane]) {
-        if (lane == 0) L.stream[0] = ctx.stream;
-        else WB_CUDA_OK(cudaStreamCreateWithFlags(&L.stream[lane], cudaStreamNonBlocking));
-    }
-    cudaStream_t s = L.stream[lane];
-    L.t0[lane] = time_us();
-    StepWs & ws = L.ws[lane];
-    if (!ensure_ws(ctx, ws, n, s)) return false;
-    const int T = rows[0].st->cross_T;
+// fills the pinned staging block of `ws` for rows[0..n) (KV slot search included, wc:2885-2897)
+static bool fill_stage(StepWs & ws, const BatchRow * rows, const SamplerRow * srows, int n) {
     const StageLayout SL = stage_layout(n);
     int * h_tok = (int *) (ws.h_stage + SL.o_tok);
     int * h_pos = (int *) (ws.h_stage + SL.o_pos);
@@ -1416,7 +1460,7 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
     for (int i = 0; i < n; ++i) {
         State * st = rows[i].st;
         KvCache & kv = st->kv_self;
-        if (!kv.find_slot(&rows[i].pos, &rows[i].seq_id, 1)) {  // wc:2885-2897
+        if (!kv.find_slot(&rows[i].pos, &rows[i].seq_id, 1)) {
             log_error("%s: failed to find a KV slot\n", __func__);
             return false;
         }
@@ -1431,10 +1475,68 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
         h_samp[i].logits_row = i;
         h_samp[i].work_slot = i;
     }
-    // Several lanes in flight: every kernel's footprint per SM is bounded so that a lane's short kernels always find room
-    // next to another lane's cross attention: two persistent CTAs per SM with a 3-deep ring (2 x 64 KB, still 97 % of the
-    // HBM peak) + a cluster GEMM CTA capped at 66 KB -- measured with tools/microbench_overlap.py, DESIGN.md 4.3.
-    const bool multi = n_lanes > 1;
+    return true;
+}
+
+bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * rows, int n, const SamplerStatic & sst, const SamplerRow * srows) {
+    WB_CUDA_OK(cudaSetDevice(ctx.model.device));
+    WB_CHECK(lane >= 0 && lane < MAX_LANES, "decode lane %d out of range\n", lane);
+    static const bool no_graph = getenv("WB200_STEP_NO_GRAPH") != nullptr;
+    g_pdl = getenv("WB200_NO_PDL") == nullptr;
+    StepLanes & L = *step_lanes(ctx);
+    if (!L.stream[lane]) {
+        if (lane == 0) L.stream[0] = ctx.stream;
+        else WB_CUDA_OK(cudaStreamCreateWithFlags(&L.stream[lane], cudaStreamNonBlocking));
+    }
+    cudaStream_t s = L.stream[lane];
+    L.t0[lane] = time_us();
+    const int T = rows[0].st->cross_T;
+    // Interleaved step (issue_step_multi): from WB200_PAIR_MIN rows per group on, the rows advance as K groups of one graph
+    int K = 1;
+    if (env_int("WB200_PAIR", 0) != 0) {  // off by default: measured gain on B200 is within 3 %
+        const int per_group = std::max(1, env_int("WB200_PAIR_MIN", 64)), k_max = std::max(1, std::min(MAX_GROUPS, env_int("WB200_GROUPS", 2)));
+        K = std::max(1, std::min(k_max, n / per_group));
+    }
+    const bool paired = K > 1;
+    StepWs * gw[MAX_GROUPS];
+    cudaStream_t gs[MAX_GROUPS];
+    int gn[MAX_GROUPS], goff[MAX_GROUPS];
+    for (int k = 0, off = 0; k < K; ++k) {
+        gn[k] = n / K + (k < n % K ? 1 : 0);
+        goff[k] = off;
+        off += gn[k];
+        L.group_n[lane][k] = gn[k];
+    }
+    L.groups[lane] = K;
+    StepWs & ws = L.ws[lane];
+    gw[0] = &ws;
+    gs[0] = s;
+    if (!ensure_ws(ctx, ws, gn[0], s)) return false;
+    for (int k = 1; k < K; ++k) {
+        StepWs & wk = L.sub[lane][k - 1];
+        if (!L.sub_stream[lane][k - 1]) WB_CUDA_OK(cudaStreamCreateWithFlags(&L.sub_stream[lane][k - 1], cudaStreamNonBlocking));
+        const uint8_t * base = wk.base;
+        if (!ensure_ws(ctx, wk, gn[k], s)) return false;
+        if (wk.base != base) destroy_graphs(ws);  // the interleaved graphs (kept with group 0) bake the other groups' pointers
+        gw[k] = &wk;
+        gs[k] = L.sub_stream[lane][k - 1];
+    }
+    if (paired) {
+        const size_t need = (size_t) K * ctx.model.hp.n_text_layer + 2;
+        while (L.events.size() < need) {
+            cudaEvent_t e = nullptr;
+            WB_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            L.events.push_back(e);
+        }
+    }
+    for (int k = 0; k < K; ++k)
+        if (!fill_stage(*gw[k], rows + goff[k], srows + goff[k], gn[k])) return false;
+
+    // More than one K/V stream's worth of kernels in flight (lanes, or the two halves of a paired step): every kernel's
+    // footprint per SM is bounded so that the short kernels always find room next to a cross attention: two persistent
+    // CTAs per SM with a 3-deep ring (2 x 64 KB, still 97 % of the HBM peak) + a cluster GEMM CTA capped at 66 KB --
+    // measured with tools/microbench_overlap.py, DESIGN.md 4.3.
+    const bool multi = n_lanes > 1 || paired;
     LaneTuning tune;
     tune.xs_ctas_per_sm = env_int("WB200_XS_CPS", 2);
     tune.xs_stages = env_int("WB200_XS_STAGES", multi ? 3 : 5);
@@ -1444,35 +1546,42 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
     static const bool tracing = getenv("WB200_STEP_TRACE") != nullptr;
     auto trace_begin = [&]() {
         if (!tracing) return;
-        if (!ws.d_trace && cudaMalloc((void **) &ws.d_trace, 2048 * sizeof(unsigned long long)) != cudaSuccess) return;
+        if (!ws.d_trace && cudaMalloc((void **) &ws.d_trace, 4096 * sizeof(unsigned long long)) != cudaSuccess) return;
         ws.trace_names.clear();
+        ws.trace_subs.clear();
         ws.trace_n = n;
         g_trace_next = ws.d_trace;
         g_trace_names = &ws.trace_names;
+        g_trace_subs = &ws.trace_subs;
+        g_trace_sub = 0;
     };
-    auto trace_end = [&]() { g_trace_next = nullptr; g_trace_names = nullptr; };
-    if (no_graph) {
-        trace_begin();
-        const bool ok = issue_step(ctx, ws, n, T, sst, s);
+    auto trace_end = [&]() { g_trace_next = nullptr; g_trace_names = nullptr; g_trace_subs = nullptr; g_trace_sub = 0; };
+    auto issue = [&]() {
+        return paired ? issue_step_multi(ctx, gw, gn, K, T, sst, gs, L.events.data()) : issue_step(ctx, ws, gn[0], T, sst, s);
+    };
+    auto reset = [&]() {
         trace_end();
         g_launch_prio = 0;
         g_tune = LaneTuning();
+    };
+    if (no_graph) {
+        trace_begin();
+        const bool ok = issue();
+        reset();
         if (!ok) return false;
     } else {
-        const uint64_t key = ((uint64_t) n << 40) | ((uint64_t) (tune.xs_ctas_per_sm & 15) << 36) | ((uint64_t) (tune.xs_stages & 15) << 32) |
-                             ((uint64_t) ((tune.wc_smem_cap >> 12) & 255) << 24) | ((uint64_t) multi << 23) | (uint32_t) (T & 0x7fffff);
+        const std::array<int, 8> key = {n, K, T, tune.xs_ctas_per_sm, tune.xs_stages, tune.wc_smem_cap, (int) multi, (int) g_pdl};
         auto it = ws.graphs.find(key);
         if (it == ws.graphs.end()) {
             const uint64_t l0 = g_step_launches.load() + kernel_launch_count();
             cudaGraph_t graph = nullptr;
             prof_suspend(true);
             trace_begin();
-            WB_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
-            const bool ok = issue_step(ctx, ws, n, T, sst, s);
-            const cudaError_t e = cudaStreamEndCapture(s, &graph);
-            trace_end();
+            cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed);
+            const bool ok = e == cudaSuccess && issue();
+            if (e == cudaSuccess) e = cudaStreamEndCapture(s, &graph);
+            reset();
             prof_suspend(false);
-            g_launch_prio = 0;
             if (!ok || e != cudaSuccess || graph == nullptr) {
                 if (graph) cudaGraphDestroy(graph);
                 log_error("%s: capturing the decode-step graph failed (%s)\n", __func__, cudaGetErrorString(e));
@@ -1490,8 +1599,7 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
             g_step_launches.fetch_sub(ge.launches - 1);
             it = ws.graphs.emplace(key, ge).first;
         }
-        g_launch_prio = 0;
-        g_tune = LaneTuning();
+        reset();
         WB_CUDA_OK(cudaGraphLaunch(it->second.exec, s));
         g_step_launches.fetch_add(it->second.launches);
     }
@@ -1507,9 +1615,11 @@ bool stage_step_wait(Context & ctx, int lane, const BatchRow * rows, int n, Deco
     StepLanes & L = *step_lanes(ctx);
     WB_CHECK(lane >= 0 && lane < MAX_LANES && L.stream[lane], "decode lane %d was never launched\n", lane);
     WB_CUDA_OK(cudaStreamSynchronize(L.stream[lane]));
-    const StepWs & ws = L.ws[lane];
-    for (int i = 0; i < n; ++i)
-        if (decs && decs[i]) decs[i]->picked = ws.h_out[i];
+    for (int k = 0, i = 0; k < L.groups[lane]; ++k) {
+        const StepWs & wk = k == 0 ? L.ws[lane] : L.sub[lane][k - 1];
+        for (int r = 0; r < L.group_n[lane][k] && i < n; ++r, ++i)
+            if (decs && decs[i]) decs[i]->picked = wk.h_out[r];
+    }
     const int64_t dt = time_us() - L.t0[lane];
     for (int i = 0; i < n; ++i) {  // wc:2982-2991: single-token decodes
         rows[i].st->t_decode_us += dt / n;
