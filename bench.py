@@ -284,21 +284,36 @@ def main():
         peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
         # estimated share of the step per category: mean sampled duration x total launches
         est = {k: (v["ms_sampled"] / max(1, v["n_sampled"])) * v["n_total"] for k, v in cats.items()}
-        dom = max(est, key=est.get) if est else None
-        roofline = None
-        if dom:
-            v = cats[dom]
+        total_est = max(1e-9, sum(est.values()))
+
+        def roof(cat):
+            v = cats[cat]
             avg_ms = v["ms_sampled"] / max(1, v["n_sampled"])
-            tensor_bound = dom in ("gemm_encoder",)
-            if tensor_bound:
+            if cat in ("gemm_encoder", "encoder_softmax") and v["flops"] > 0:
                 ach = v["flops"] / (v["ms_sampled"] / 1e3) / 1e12
-                roofline = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak}
+                r = {"kernel": cat, "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak}
             else:
-                ach = v["bytes"] / (v["ms_sampled"] / 1e3) / 1e9
-                roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
-            roofline.update({"traffic": None, "avg_launch_ms": avg_ms, "launches_sampled": v["n_sampled"], "peak_source": peak_src,
-                             "share_of_step_est": est[dom] / max(1e-9, sum(est.values())),
-                             "algorithmic_bytes_per_launch": v["bytes"] / max(1, v["n_sampled"])})
+                ach = v["bytes"] / max(1e-12, v["ms_sampled"] / 1e3) / 1e9
+                r = {"kernel": cat, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
+            r.update({"traffic": None, "avg_launch_ms": avg_ms, "launches_sampled": v["n_sampled"], "launches_total": v["n_total"],
+                      "peak_source": peak_src, "share_of_step_est": est[cat] / total_est,
+                      "algorithmic_bytes_per_launch": v["bytes"] / max(1, v["n_sampled"]),
+                      "algorithmic_flops_per_launch": v["flops"] / max(1, v["n_sampled"])})
+            return r
+
+        ranked = sorted(est, key=est.get, reverse=True)
+        roofline = roof(ranked[0]) if ranked else None
+        if roofline:
+            # DRAM bytes per launch of the same kernel from the committed `ncu --set full` capture (profiles/), when it was taken at this batch
+            try:
+                tr = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text())
+                ent = tr.get(roofline["kernel"], {})
+                if ent.get("batch_per_gpu") == B and ent.get("model") == args.model:
+                    roofline["traffic"] = ent["dram_bytes_per_launch"]
+                    roofline["traffic_source"] = ent.get("source")
+            except Exception:
+                pass
+        roofline_next = [roof(c) for c in ranked[1:4]]
         out = {
             "metric": "RTFx (audio-s/s) greedy", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -312,6 +327,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
             "roofline": roofline,
+            "roofline_next": roofline_next,
             "phase_ms_per_step_host_clock": phase,
             "kernel_breakdown_ms_per_step_est": {k: round(x / args.steps, 3) for k, x in sorted(est.items(), key=lambda kv: -kv[1])},
         }

@@ -21,8 +21,22 @@ struct Cat {
 std::mutex g_mu;
 int g_max = 0;
 int g_suspended = 0;
+uint64_t * g_capture_counts = nullptr;
 Cat g_cat[PC_COUNT];
 }  // namespace
+
+bool prof_enabled() { return g_max > 0; }
+
+void prof_capture_counts(uint64_t * counts) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_capture_counts = counts;
+}
+
+void prof_add_totals(const uint64_t * counts) {
+    if (g_max <= 0) return;
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int k = 0; k < PC_COUNT; ++k) g_cat[k].total += counts[k];
+}
 
 void prof_enable(int max_samples_per_cat) {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -44,6 +58,10 @@ void prof_reset() {
 }
 
 ProfScope::ProfScope(int cat_, cudaStream_t s_, double bytes, double flops) : cat(cat_), s(s_), slot(-1) {
+    if (g_capture_counts != nullptr) {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (g_capture_counts != nullptr && g_suspended > 0) g_capture_counts[cat]++;
+    }
     if (g_max <= 0) return;
     std::lock_guard<std::mutex> lk(g_mu);
     if (g_suspended > 0) return;

@@ -16,6 +16,11 @@ const char * prof_cat_name(int cat);
 void prof_enable(int max_samples_per_cat);  // 0 disables
 void prof_reset();
 void prof_suspend(bool on);  // no event records while a stream capture is in progress
+bool prof_enabled();
+// Graph replays: while `counts` (PC_COUNT entries) is set, scopes opened under prof_suspend only count their category there;
+// prof_add_totals adds such a tally to the launch totals each time the captured graph is replayed.
+void prof_capture_counts(uint64_t * counts);
+void prof_add_totals(const uint64_t * counts);
 // returns sampled-milliseconds sum, sampled count and total launch count per category (arrays of PC_COUNT)
 void prof_collect(double * ms_sum, uint64_t * n_sampled, uint64_t * n_total, double * bytes_sampled, double * flops_sampled);
 

@@ -497,6 +497,7 @@ static bool gemm_wstream(const __half * W, const __half * X, int n, int N_out, i
     a.tmem_cols = p.tmem_cols;
     a.trace = trace_slot(N_out > 20000 ? "logits" : "gemm_ws");
     if (split_out) *split_out = p.split;
+    ProfScope prof_scope(N_out > 20000 ? PC_GEMM_LOGITS : PC_GEMM_DEC, s, (double) N_out * K * 2 + (double) n * K * 2);
     return launch_k(gemm_wstream_kernel, dim3(p.tiles, p.split), dim3(WS_THREADS), (size_t) p.smem, s, pdl, tw, tx, a);
 }
 
@@ -553,6 +554,7 @@ static bool gemm_wcluster(const __half * W, const __half * X, int n, int N_out, 
     a.mode = o.mode; a.out = o.out; a.ldo = o.ldo; a.bias = o.bias; a.scale = o.scale; a.scale_f1 = o.scale_f1;
     a.gelu_table = o.gelu_table; a.tmem_cols = p.tmem_cols; a.tok_per_rank = p.tok_per_rank;
     a.trace = trace_slot(N_out == 3 * K ? "gemm_qkv" : N_out == 4 * K ? "gemm_fc1" : K == 4 * N_out ? "gemm_fc2" : "gemm_sq");
+    ProfScope prof_scope(PC_GEMM_DEC, s, (double) N_out * K * 2 + (double) n * K * 2);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.split, p.tiles);
     cfg.blockDim = dim3(WS_THREADS);
@@ -1075,6 +1077,8 @@ static bool launch_cross(CrossArgs a, int n_rows, cudaStream_t s, bool pdl) {
     a.trace = trace_slot("cross");
     a.stages = std::max(2, std::min(g_tune.xs_stages, 8));
     const int grid = std::min(a.items, step_sm_count() * std::max(1, g_tune.xs_ctas_per_sm));
+    // algorithmic bytes: the K and V panels of every (row, head), f16
+    ProfScope prof_scope(PC_CROSS_ATTN, s, (double) a.items * a.T * 64 * 2 * 2, (double) a.items * a.T * 64 * 4);
     return launch_k(cross_attn_step_kernel, dim3(grid), dim3(XS_THREADS), (size_t) xs_smem_bytes(a.T, a.stages), s, pdl, a);
 }
 
@@ -1086,6 +1090,7 @@ namespace {
 struct GraphEntry {
     cudaGraphExec_t exec = nullptr;
     uint64_t launches = 0;
+    uint64_t cat_counts[PC_COUNT] = {};  // launches per profiler category in one replay
 };
 
 struct StepWs {
@@ -1217,6 +1222,7 @@ struct LaneIssue {
         a.te = embed ? m.d_te : nullptr; a.pe = m.d_pe; a.tokens = d_tok; a.pos = d_pos;
         a.x_out = ws.x; a.xa_out = ws.xa; a.gamma = nm.g; a.beta = nm.b; a.eps = m.hp.eps; a.S = S;
         a.trace = trace_slot("ln");
+        ProfScope prof_scope(PC_LN, s, (double) n * S * 10);
         return launch_k(ln_reduce_kernel, dim3(n), dim3(LN_THREADS), 0, s, !embed, a);
     }
     // staging upload + token/position embedding + first LayerNorm
@@ -1242,6 +1248,7 @@ struct LaneIssue {
             SelfArgs a{};
             a.qkv16 = ws.qkv16; a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
             a.trace = trace_slot("self");
+            ProfScope prof_scope(PC_SELF_ATTN, s);
             if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), (size_t) 5120 * 4, s, true, a)) return false;
         }
         {   // x += Wo.att + bo (wc:2657-2664)
@@ -1363,6 +1370,7 @@ struct StepLanes {
     int groups[MAX_LANES] = {};                       // groups of the step in flight
     int group_n[MAX_LANES][MAX_GROUPS] = {};          // and their row counts
     int64_t t0[MAX_LANES] = {};
+    uint64_t step_no[MAX_LANES] = {};
     std::vector<cudaEvent_t> events;      // fork/join and the cross-attention chain of the paired graph
     int prio_hi = 0;
 };
@@ -1564,30 +1572,41 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
         g_launch_prio = 0;
         g_tune = LaneTuning();
     };
-    if (no_graph) {
+    // with the in-situ profiler on (bench.py), every 16th step of a lane is issued live so that CUDA events on the launching
+    // stream time its kernels inside the real run (graph nodes cannot be bracketed by events without breaking the graph)
+    // The sampled step runs with the device to itself (the other lanes are drained first and it is waited for here), so the
+    // event pairs bracket each kernel alone -- its own speed, not its share of a machine contended by the other lanes.
+    const bool live_sample = prof_enabled() && (L.step_no[lane]++ % 128) == 7;
+    if (live_sample)
+        for (int l = 0; l < MAX_LANES; ++l)
+            if (l != lane && L.stream[l]) WB_CUDA_OK(cudaStreamSynchronize(L.stream[l]));
+    if (no_graph || live_sample) {
         trace_begin();
         const bool ok = issue();
         reset();
         if (!ok) return false;
+        if (live_sample) WB_CUDA_OK(cudaStreamSynchronize(s));
     } else {
         const std::array<int, 8> key = {n, K, T, tune.xs_ctas_per_sm, tune.xs_stages, tune.wc_smem_cap, (int) multi, (int) g_pdl};
         auto it = ws.graphs.find(key);
         if (it == ws.graphs.end()) {
             const uint64_t l0 = g_step_launches.load() + kernel_launch_count();
             cudaGraph_t graph = nullptr;
+            GraphEntry ge;
             prof_suspend(true);
+            prof_capture_counts(ge.cat_counts);
             trace_begin();
             cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed);
             const bool ok = e == cudaSuccess && issue();
             if (e == cudaSuccess) e = cudaStreamEndCapture(s, &graph);
             reset();
+            prof_capture_counts(nullptr);
             prof_suspend(false);
             if (!ok || e != cudaSuccess || graph == nullptr) {
                 if (graph) cudaGraphDestroy(graph);
                 log_error("%s: capturing the decode-step graph failed (%s)\n", __func__, cudaGetErrorString(e));
                 return false;
             }
-            GraphEntry ge;
             ge.launches = g_step_launches.load() + kernel_launch_count() - l0;
             const cudaError_t ei = cudaGraphInstantiate(&ge.exec, graph, 0);
             cudaGraphDestroy(graph);
@@ -1602,6 +1621,7 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
         reset();
         WB_CUDA_OK(cudaGraphLaunch(it->second.exec, s));
         g_step_launches.fetch_add(it->second.launches);
+        prof_add_totals(it->second.cat_counts);
     }
     return true;
 }
