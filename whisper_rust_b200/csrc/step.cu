@@ -345,32 +345,49 @@ gemm_wcluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
         const bool f_ok = f < a.N_out;
         if (a.bias != nullptr && f_ok) bias = __ldg((const float4 *) (a.bias + f));
         const float sc = (f < a.scale_f1) ? a.scale : 1.0f;
+        // two tokens per iteration, all of their split partials requested before the first add: the distributed-shared-memory
+        // round trips overlap instead of queueing behind each other (the sums keep the split order: results are unchanged)
 #pragma unroll 1
-        for (int t = t0 + (e >> 5); t < t1; t += 4) {
-            float4 v = ld_dsmem_f4(p_local + (uint32_t) t * 512u, 0);
-            for (int s = 1; s < a.split; ++s) {
-                const float4 w = ld_dsmem_f4(p_local + (uint32_t) t * 512u, (uint32_t) s);
-                v.x = __fadd_rn(v.x, w.x); v.y = __fadd_rn(v.y, w.y); v.z = __fadd_rn(v.z, w.z); v.w = __fadd_rn(v.w, w.w);
+        for (int tb = t0 + (e >> 5); tb < t1; tb += 8) {
+            float4 w[2][8];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int t = tb + 4 * u;
+#pragma unroll
+                for (int s = 0; s < 8; ++s)
+                    if (t < t1 && s < a.split) w[u][s] = ld_dsmem_f4(p_local + (uint32_t) t * 512u, (uint32_t) s);
             }
-            if (!f_ok) continue;
-            v.x = __fadd_rn(v.x, bias.x); v.y = __fadd_rn(v.y, bias.y); v.z = __fadd_rn(v.z, bias.z); v.w = __fadd_rn(v.w, bias.w);
-            if (a.mode == WC_RESIDUAL) {
-                float4 * xp = (float4 *) ((float *) a.out + (int64_t) t * a.ldo + f);
-                const float4 x = *xp;
-                v.x = __fadd_rn(v.x, x.x); v.y = __fadd_rn(v.y, x.y); v.z = __fadd_rn(v.z, x.z); v.w = __fadd_rn(v.w, x.w);
-                *xp = v;
-            } else {
-                if (a.mode == WC_GELU) {
-                    v.x = gelu_f16table(v.x, a.gelu_table); v.y = gelu_f16table(v.y, a.gelu_table);
-                    v.z = gelu_f16table(v.z, a.gelu_table); v.w = gelu_f16table(v.w, a.gelu_table);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int t = tb + 4 * u;
+                if (t >= t1) break;
+                float4 v = w[u][0];
+#pragma unroll
+                for (int s = 1; s < 8; ++s)
+                    if (s < a.split) {
+                        v.x = __fadd_rn(v.x, w[u][s].x); v.y = __fadd_rn(v.y, w[u][s].y);
+                        v.z = __fadd_rn(v.z, w[u][s].z); v.w = __fadd_rn(v.w, w[u][s].w);
+                    }
+                if (!f_ok) continue;
+                v.x = __fadd_rn(v.x, bias.x); v.y = __fadd_rn(v.y, bias.y); v.z = __fadd_rn(v.z, bias.z); v.w = __fadd_rn(v.w, bias.w);
+                if (a.mode == WC_RESIDUAL) {
+                    float4 * xp = (float4 *) ((float *) a.out + (int64_t) t * a.ldo + f);
+                    const float4 x = *xp;
+                    v.x = __fadd_rn(v.x, x.x); v.y = __fadd_rn(v.y, x.y); v.z = __fadd_rn(v.z, x.z); v.w = __fadd_rn(v.w, x.w);
+                    *xp = v;
                 } else {
-                    v.x = __fmul_rn(v.x, sc); v.y = __fmul_rn(v.y, sc); v.z = __fmul_rn(v.z, sc); v.w = __fmul_rn(v.w, sc);
+                    if (a.mode == WC_GELU) {
+                        v.x = gelu_f16table(v.x, a.gelu_table); v.y = gelu_f16table(v.y, a.gelu_table);
+                        v.z = gelu_f16table(v.z, a.gelu_table); v.w = gelu_f16table(v.w, a.gelu_table);
+                    } else {
+                        v.x = __fmul_rn(v.x, sc); v.y = __fmul_rn(v.y, sc); v.z = __fmul_rn(v.z, sc); v.w = __fmul_rn(v.w, sc);
+                    }
+                    const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+                    uint2 pk;
+                    pk.x = *(const uint32_t *) &h0;
+                    pk.y = *(const uint32_t *) &h1;
+                    *(uint2 *) ((__half *) a.out + (int64_t) t * a.ldo + f) = pk;
                 }
-                const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
-                uint2 pk;
-                pk.x = *(const uint32_t *) &h0;
-                pk.y = *(const uint32_t *) &h1;
-                *(uint2 *) ((__half *) a.out + (int64_t) t * a.ldo + f) = pk;
             }
         }
     }
@@ -1115,6 +1132,7 @@ struct StepWs {
     std::vector<const char *> trace_names;
     std::vector<int> trace_subs;
     int trace_n = 0;                         // rows of the traced step
+    int kv_cells_max = 0;                    // largest self-KV cache (cells) among the staged rows: sizes self_attn_step's score buffer
 };
 
 struct StageLayout {
@@ -1190,6 +1208,16 @@ bool ensure_ws(Context & ctx, StepWs & ws, int n, cudaStream_t stream) {
     return true;
 }
 
+// Calibration of the sampled live steps: an event pair around a kernel that does nothing measures what the bracketing itself
+// adds to every sampled launch (event records + an unoverlapped launch); bench.py subtracts it from the per-kernel averages.
+__global__ void null_kernel() {}
+static void prof_calibrate(cudaStream_t s) {
+    for (int i = 0; i < 8; ++i) {
+        ProfScope prof_scope(PC_CALIB, s);
+        null_kernel<<<1, 32, 0, s>>>();
+    }
+}
+
 // The launches of one decode step for the n rows of one workspace, in the pieces the two issue orders below need.
 struct LaneIssue {
     Context & ctx;
@@ -1222,7 +1250,7 @@ struct LaneIssue {
         a.te = embed ? m.d_te : nullptr; a.pe = m.d_pe; a.tokens = d_tok; a.pos = d_pos;
         a.x_out = ws.x; a.xa_out = ws.xa; a.gamma = nm.g; a.beta = nm.b; a.eps = m.hp.eps; a.S = S;
         a.trace = trace_slot("ln");
-        ProfScope prof_scope(PC_LN, s, (double) n * S * 10);
+        ProfScope prof_scope(PC_LN_DEC, s, (double) n * S * 10);
         return launch_k(ln_reduce_kernel, dim3(n), dim3(LN_THREADS), 0, s, !embed, a);
     }
     // staging upload + token/position embedding + first LayerNorm
@@ -1249,7 +1277,10 @@ struct LaneIssue {
             a.qkv16 = ws.qkv16; a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
             a.trace = trace_slot("self");
             ProfScope prof_scope(PC_SELF_ATTN, s);
-            if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), (size_t) 5120 * 4, s, true, a)) return false;
+            // the score buffer only has to hold the cache's cells (step_eligible bounds them by 5000): 2 KB instead of 20 KB for
+            // the greedy cache of 512 cells, which lifts the kernel from 9 to 16 resident CTAs per SM
+            const size_t sc_bytes = (size_t) std::min(5120, std::max(256, (int) pad_to(ws.kv_cells_max, 64))) * 4;
+            if (!launch_k(self_attn_step_kernel, dim3(H, n), dim3(128), sc_bytes, s, true, a)) return false;
         }
         {   // x += Wo.att + bo (wc:2657-2664)
             WcOut o{};
@@ -1465,6 +1496,7 @@ static bool fill_stage(StepWs & ws, const BatchRow * rows, const SamplerRow * sr
     SelfKvRow * h_self = (SelfKvRow *) (ws.h_stage + SL.o_self);
     CrossKvRow * h_cross = (CrossKvRow *) (ws.h_stage + SL.o_cross);
     SamplerRow * h_samp = (SamplerRow *) (ws.h_stage + SL.o_samp);
+    ws.kv_cells_max = 0;
     for (int i = 0; i < n; ++i) {
         State * st = rows[i].st;
         KvCache & kv = st->kv_self;
@@ -1478,6 +1510,7 @@ static bool fill_stage(StepWs & ws, const BatchRow * rows, const SamplerRow * sr
         SelfKvRow & sr = h_self[i];
         sr.k_base = kv.k; sr.v_base = kv.v; sr.cells = nullptr;
         sr.n_cells = kv.head + 1; sr.store_cell = kv.head; sr.n_ctx = kv.size;
+        ws.kv_cells_max = std::max(ws.kv_cells_max, kv.size);
         h_cross[i] = CrossKvRow{st->kv_cross, nullptr, 0, 0};
         h_samp[i] = srows[i];
         h_samp[i].logits_row = i;
@@ -1582,12 +1615,15 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
             if (l != lane && L.stream[l]) WB_CUDA_OK(cudaStreamSynchronize(L.stream[l]));
     if (no_graph || live_sample) {
         trace_begin();
+        if (live_sample) prof_calibrate(s);
         const bool ok = issue();
         reset();
         if (!ok) return false;
         if (live_sample) WB_CUDA_OK(cudaStreamSynchronize(s));
     } else {
-        const std::array<int, 8> key = {n, K, T, tune.xs_ctas_per_sm, tune.xs_stages, tune.wc_smem_cap, (int) multi, (int) g_pdl};
+        int cells = 0;
+        for (int k = 0; k < K; ++k) cells = std::max(cells, (int) pad_to(gw[k]->kv_cells_max, 64));
+        const std::array<int, 8> key = {n, K, T, tune.xs_ctas_per_sm, tune.xs_stages * 16 + (int) multi * 2 + (int) g_pdl, tune.wc_smem_cap, cells, 0};
         auto it = ws.graphs.find(key);
         if (it == ws.graphs.end()) {
             const uint64_t l0 = g_step_launches.load() + kernel_launch_count();
