@@ -177,6 +177,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device — the b200 arm has no CPU path (use --impl reference for the CPU engine)")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries exactly one JSON line (rank 0)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():

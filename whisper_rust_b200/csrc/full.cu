@@ -893,6 +893,7 @@ int lang_auto_detect(Context * ctx, State * st, int offset_ms, float * lang_prob
 // --------------------------------------------------------------------------------------------
 int full_with_states(Context * ctx, State * const * states, int n_states, const whisper_full_params * params_arr, bool params_per_state,
                      const float * const * samples, const int * n_samples) {
+    const int64_t t_call0 = time_us();
     const whisper_full_params & params_in = params_arr[0];  // suppress rules / strategy are shared by the batch
     if (cudaSetDevice(ctx->model.device) != cudaSuccess) return -6;
     std::vector<FullJob> jobs((size_t) n_states);
@@ -952,7 +953,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 }
             }
         if (ln.enc_jobs.empty()) return;
-        if (getenv("WB200_HOST_PROF")) fprintf(stderr, "host_prof: encode %zu windows\n", ln.enc_jobs.size());
+        if (getenv("WB200_HOST_PROF")) fprintf(stderr, "host_prof: t=%.1f ms encode %zu windows\n", (time_us() - t_call0) / 1e3, ln.enc_jobs.size());
         if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
             log_error("%s: failed to encode\n", __func__);
             for (auto * j : ln.enc_jobs) j->finish(-6);
@@ -971,6 +972,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     const bool host_prof = getenv("WB200_HOST_PROF") != nullptr;
     int64_t hp_gather = 0, hp_elig = 0, hp_launch = 0, hp_wait = 0, hp_after = 0, hp_steps = 0;
     std::string hp_log;
+    int hp_last_n[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
     // advances a lane until it has a fused step in flight (pending) or nothing left to do
     auto lane_advance = [&](Lane & ln, int lane_id) {
         while (true) {
@@ -1030,7 +1032,13 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             if (fused_step) {
                 // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
                 ok = stage_step_launch(*ctx, lane_id, n_lanes, ln.rows.data(), n_rows, sst, ln.srows.data());
-                if (host_prof) hp_launch += time_us() - tg2, ++hp_steps, hp_log += " " + std::to_string(n_rows);
+                if (host_prof) {
+                    hp_launch += time_us() - tg2, ++hp_steps;
+                    if (n_rows != hp_last_n[lane_id & 7]) {  // log changes of a lane's row count with their time
+                        hp_log += " [t=" + std::to_string((time_us() - t_call0) / 1000) + "ms lane" + std::to_string(lane_id) + " n=" + std::to_string(n_rows) + "]";
+                        hp_last_n[lane_id & 7] = n_rows;
+                    }
+                }
                 if (ok) {
                     ln.pending = true;
                     return;
@@ -1085,7 +1093,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         if (any_pending && !served) std::this_thread::yield();
         if (!any_pending) break;
     }
-    if (host_prof) fprintf(stderr, "host_prof: rows per step:%s\n", hp_log.c_str());
+    if (host_prof) fprintf(stderr, "host_prof: total %.1f ms; row-count changes:%s\n", (time_us() - t_call0) / 1e3, hp_log.c_str());
     if (host_prof)
         fprintf(stderr, "host_prof: %lld fused steps; us/step: gather %.1f eligible %.1f launch %.1f wait %.1f after_device %.1f\n", (long long) hp_steps,
                 hp_gather / (double) std::max<int64_t>(1, hp_steps), hp_elig / (double) std::max<int64_t>(1, hp_steps),
