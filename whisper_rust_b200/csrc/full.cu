@@ -973,10 +973,29 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     int64_t hp_gather = 0, hp_elig = 0, hp_launch = 0, hp_wait = 0, hp_after = 0, hp_steps = 0;
     std::string hp_log;
     int hp_last_n[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
+    // Jobs that come back for a later window of their audio (seek advanced by less than the window) have fallen out of step
+    // with their lane; instead of each decoding alone on its own lane they are handed to lane 0, which runs them as one batch.
+    std::vector<FullJob *> adopt;
     // advances a lane until it has a fused step in flight (pending) or nothing left to do
     auto lane_advance = [&](Lane & ln, int lane_id) {
         while (true) {
             const int64_t tg0 = host_prof ? time_us() : 0;
+            if (n_lanes > 1) {
+                if (lane_id == 0) {
+                    ln.jobs.insert(ln.jobs.end(), adopt.begin(), adopt.end());
+                    adopt.clear();
+                } else {
+                    for (size_t q = 0; q < ln.jobs.size();) {
+                        FullJob * j = ln.jobs[q];
+                        if (j->phase == FullJob::WINDOW_BEGIN && j->seek > j->seek_start && j->seek + FullJob::delta_min < j->seek_end) {
+                            adopt.push_back(j);
+                            ln.jobs.erase(ln.jobs.begin() + (long) q);
+                        } else {
+                            ++q;
+                        }
+                    }
+                }
+            }
             // ---- windows that need their encoder pass
             encode_jobs(ln, {&ln});
             // ---- gather the decoder rows of every live job
@@ -985,13 +1004,25 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             ln.sdecs.clear();
             ln.dev_jobs.clear();
             bool any_live = false, any_dists = false;
+            // Jobs that contribute several rows (prompt passes, beams) take the general decoder path, jobs with one row per
+            // state the fused step.  When both kinds are waiting, the multi-row jobs go first on their own: which path a
+            // token is computed on then depends on the job alone, never on what else happens to share the iteration.
+            bool has_multi = false, has_single = false;
+            for (FullJob * jp : ln.jobs) {
+                FullJob & j = *jp;
+                if (j.phase == FullJob::DONE) continue;
+                if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
+                if ((j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) || j.rows.empty()) continue;
+                if (j.rows.size() == 1 && j.srows.size() == 1) has_single = true;
+                else has_multi = true;
+            }
             for (FullJob * jp : ln.jobs) {
                 FullJob & j = *jp;
                 if (j.phase == FullJob::DONE) continue;
                 any_live = true;
-                if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
                 if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
                 if (j.rows.empty()) continue;
+                if (has_multi && has_single && j.rows.size() == 1 && j.srows.size() == 1) continue;  // waits for the next iteration
                 // flagged rows of this job map to consecutive logits rows
                 int flagged = 0;
                 for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
@@ -1090,8 +1121,11 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             lane_complete(ln, l);
             lane_advance(ln, l);
         }
-        if (any_pending && !served) std::this_thread::yield();
+        if (!adopt.empty() && !lanes[0].pending) lane_advance(lanes[0], 0);
+        any_pending = false;
+        for (int l = 0; l < n_lanes; ++l) any_pending = any_pending || lanes[(size_t) l].pending;
         if (!any_pending) break;
+        if (!served) std::this_thread::yield();
     }
     if (host_prof) fprintf(stderr, "host_prof: total %.1f ms; row-count changes:%s\n", (time_us() - t_call0) / 1e3, hp_log.c_str());
     if (host_prof)
