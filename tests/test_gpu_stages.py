@@ -171,3 +171,33 @@ def test_full_greedy_tokens_match_oracle(prod_lib, ref_lib, arch, recipe, second
     a = _run_full(ref_lib, False, arch, pcm, recipe=recipe, best_of=1)
     b = _run_full(prod_lib, True, arch, pcm, recipe=recipe, best_of=1)
     _same(a, b)
+
+
+def test_logits_filter_callback_matches_oracle(prod_lib, ref_lib):
+    """logits_filter_callback (wh:474-480) sees HOST logits after the static suppressions and before the timestamp rules
+    (wc:6226-6228) and may mutate them: same callback on both engines -> same transcript, same number of calls."""
+    pcm = synth.synth_audio(47.3, seed=26)   # two windows, ~230 tokens
+    out = {}
+    for name, lib, gpu in (("ref", ref_lib, False), ("b200", prod_lib, True)):
+        calls = []
+
+        def cb(ctx, state, tokens, n_tokens, logits, ud, calls=calls):
+            calls.append((n_tokens, tokens[n_tokens - 1].id if n_tokens else -1))
+            if n_tokens % 5 == 2:
+                logits[1000 + n_tokens] += 40.0          # force a token
+            for k in range(2000, 2064):
+                logits[k] = -float("inf")                # suppress a range
+            if n_tokens == 0:
+                assert logits[50257] == -float("inf")    # suppress_blank already applied to <|eot|> at the first step
+
+        ctx = WhisperContext.new_from_buffer_with_params(model_blob("mini", RICH), WhisperContextParameters(use_gpu=gpu), lib=lib)
+        st = ctx.create_state()
+        p = FullParams(lib, SamplingStrategy.GREEDY, best_of=1)
+        p.set_n_threads(8).set_language("en").set_temperature_inc(0.0).set_logits_filter_callback(cb)
+        assert st.full(p, pcm) == 0
+        out[name] = (st.segments(), calls)
+        st.free(); ctx.free()
+    _same(out["ref"][0], out["b200"][0])
+    assert out["ref"][1] == out["b200"][1] and len(out["ref"][1]) > 10
+    ids = [t["id"] for s in out["b200"][0] for t in s.tokens]
+    assert any(1000 <= i < 1300 for i in ids) and not any(2000 <= i < 2064 for i in ids)

@@ -233,7 +233,7 @@ Context * context_create(whisper_model_loader * loader, whisper_context_params p
         delete ctx;
         return nullptr;
     }
-    if (cudaMalloc((void **) &ctx->d_suppress, (size_t) ctx->model.hp.n_vocab) != cudaSuccess) {
+    if (cudaMalloc((void **) &ctx->d_suppress, 2 * (size_t) ctx->model.hp.n_vocab) != cudaSuccess) {
         delete ctx;
         return nullptr;
     }
@@ -804,7 +804,8 @@ bool stage_fetch_logits(Context & ctx, const BatchRow * rows, int n) {
     return true;
 }
 
-bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * srows, int n, bool copy_dists, Decoder ** decs) {
+bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * srows, int n, bool copy_dists, Decoder ** decs,
+                  const std::function<void(int, float *)> * prefilter) {
     if (n <= 0) return true;
     DecWorkspace & ws = ctx.dec_ws;
     const int V = ctx.model.hp.n_vocab;
@@ -814,6 +815,18 @@ bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * s
     const size_t o = ws.stage_bytes - (((size_t) n * sizeof(SamplerRow) + 15) & ~(size_t) 15);
     memcpy(ws.h_stage + o, srows, (size_t) n * sizeof(SamplerRow));
     WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage + o, ws.h_stage + o, (size_t) n * sizeof(SamplerRow), cudaMemcpyHostToDevice, s));
+    if (prefilter) {
+        // the callback mutates HOST logits (wh:474-480): one D2H / H2D round trip per flagged row, only when a callback is set
+        std::vector<float> host((size_t) V);
+        for (int i = 0; i < n; ++i) {
+            if (!srows[i].prefiltered) continue;
+            WB_CUDA_OK(cudaMemcpyAsync(host.data(), ws.logits + (size_t) srows[i].logits_row * V, (size_t) V * 4, cudaMemcpyDeviceToHost, s));
+            WB_CUDA_OK(cudaStreamSynchronize(s));
+            (*prefilter)(i, host.data());
+            WB_CUDA_OK(cudaMemcpyAsync(ws.samp_work + (size_t) srows[i].work_slot * 3 * V, host.data(), (size_t) V * 4, cudaMemcpyHostToDevice, s));
+            WB_CUDA_OK(cudaStreamSynchronize(s));
+        }
+    }
     if (!sample_rows(sst, ws.logits, V, (const SamplerRow *) (ws.d_stage + o), n, ws.samp_work, ws.d_out, s)) return false;
     WB_CUDA_OK(cudaMemcpyAsync(ws.h_out, ws.d_out, (size_t) n * sizeof(SamplerOut), cudaMemcpyDeviceToHost, s));
     if (copy_dists) {

@@ -4,6 +4,7 @@
 // whisper_encode_internal wc:2376-2472, whisper_decode_internal wc:2864-2994.
 #pragma once
 
+#include <functional>
 #include <mutex>
 #include <random>
 #include <set>
@@ -164,8 +165,9 @@ struct Context {
     std::vector<std::vector<int>> ahead_slot;  // [L][H]
     int * d_ahead_slot = nullptr;              // [L][H]
 
-    uint8_t * d_suppress = nullptr;            // [V] scratch for the per-call suppress mask
-    std::vector<uint8_t> suppress_host;
+    uint8_t * d_suppress = nullptr;            // [2][V] per-call suppress masks: everything | the part that follows logits_filter_callback
+    std::vector<uint8_t> suppress_host;        // everything
+    std::vector<uint8_t> suppress_pre_host;    // the part the reference applies before logits_filter_callback (wc:6197-6224)
 
     ~Context();
 };
@@ -198,7 +200,10 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n_rows, bool save_qk
 // copy flagged logits rows to the states' host `logits` vectors ([n_tokens][V] per state)
 bool stage_fetch_logits(Context & ctx, const BatchRow * rows, int n_rows);
 // run the device sampler over flagged rows; results land in ctx.dec_ws.h_out[0..n_flagged)
-bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * srows, int n, bool copy_dists, Decoder ** decs);
+// `prefilter` (logits_filter_callback): rows with srows[i].prefiltered get their raw logits row on the host, the callee filters it in
+// place (temperature, pre-callback suppressions, the user's callback), and the result becomes the sampler's input for that row.
+bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * srows, int n, bool copy_dists, Decoder ** decs,
+                  const std::function<void(int, float *)> * prefilter = nullptr);
 
 bool build_suppress_mask(Context & ctx, const whisper_full_params & params);
 

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <thread>
 #include <map>
 #include <regex>
@@ -46,6 +47,7 @@ bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
     kill(vc.token_transcribe);
     kill(vc.token_prev);
     for (int i = 0; i < 100; ++i) kill(vc.token_sot + 1 + i);  // whisper_token_lang over the whole language table (wc:6219-6221)
+    ctx.suppress_pre_host = mk;  // everything above precedes logits_filter_callback in the reference (wc:6226-6228); what follows comes after it
     if (params.suppress_regex != nullptr) {
         try {
             std::regex re(params.suppress_regex);
@@ -68,7 +70,10 @@ bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
         auto i2 = vc.token_to_id.find(" '");
         if (i2 != vc.token_to_id.end()) kill(i2->second);
     }
+    std::vector<uint8_t> post((size_t) V);
+    for (int i = 0; i < V; ++i) post[(size_t) i] = mk[(size_t) i] && !ctx.suppress_pre_host[(size_t) i];
     WB_CUDA_OK(cudaMemcpyAsync(ctx.d_suppress, mk.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream));
+    WB_CUDA_OK(cudaMemcpyAsync(ctx.d_suppress + V, post.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream));
     WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
     return true;
 }
@@ -77,6 +82,7 @@ static SamplerStatic sampler_static(Context & ctx) {
     const Vocab & vc = ctx.model.vocab;
     SamplerStatic s{};
     s.suppress = ctx.d_suppress;
+    s.suppress_post = ctx.d_suppress + vc.n_vocab;
     s.n_vocab = vc.n_vocab;
     s.token_eot = vc.token_eot;
     s.token_beg = vc.token_beg;
@@ -927,6 +933,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
         std::vector<BatchRow> rows;
         std::vector<SamplerRow> srows;
         std::vector<Decoder *> sdecs;
+        std::vector<FullJob *> sjobs;  // the job behind every sampler row
         bool pending = false;
     };
     int n_lanes = 1;
@@ -1002,6 +1009,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             ln.rows.clear();
             ln.srows.clear();
             ln.sdecs.clear();
+            ln.sjobs.clear();
             ln.dev_jobs.clear();
             bool any_live = false, any_dists = false;
             // Jobs that contribute several rows (prompt passes, beams) take the general decoder path, jobs with one row per
@@ -1013,7 +1021,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 if (j.phase == FullJob::DONE) continue;
                 if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
                 if ((j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) || j.rows.empty()) continue;
-                if (j.rows.size() == 1 && j.srows.size() == 1) has_single = true;
+                if (j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback) has_single = true;
                 else has_multi = true;
             }
             for (FullJob * jp : ln.jobs) {
@@ -1022,7 +1030,8 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 any_live = true;
                 if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
                 if (j.rows.empty()) continue;
-                if (has_multi && has_single && j.rows.size() == 1 && j.srows.size() == 1) continue;  // waits for the next iteration
+                if (has_multi && has_single && j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback)
+                    continue;  // waits for the next iteration
                 // flagged rows of this job map to consecutive logits rows
                 int flagged = 0;
                 for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
@@ -1037,8 +1046,10 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                     SamplerRow sr = j.srows[q];
                     sr.logits_row = base + (int) q;
                     sr.work_slot = base + (int) q;
+                    sr.prefiltered = j.params.logits_filter_callback ? 1 : 0;
                     ln.srows.push_back(sr);
                     ln.sdecs.push_back(j.sdecs[q]);
+                    ln.sjobs.push_back(&j);
                     any_dists = any_dists || j.sdecs[q]->want_dists;
                 }
                 ln.dev_jobs.push_back(&j);
@@ -1046,16 +1057,33 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
             if (!any_live) return;
             if (ln.dev_jobs.empty()) continue;
 
-            if (params_in.logits_filter_callback) {
-                // the callback sees host logits between the static suppressions and the timestamp rules (wc:6226-6228):
-                // not supported on the device sampler path
-                static bool warned = false;
-                if (!warned) log_msg(GGML_LOG_LEVEL_WARN, "%s: logits_filter_callback is ignored by the device sampler\n", __func__);
-                warned = true;
-            }
+            // logits_filter_callback (wh:474-480, wc:6226-6228) mutates HOST logits between the static suppressions and the
+            // timestamp rules: those rows take the general path, the host applies everything the reference applies before the
+            // callback, calls it, and the device sampler continues from there (SamplerRow::prefiltered)
+            bool any_callback = false;
+            for (const SamplerRow & sr : ln.srows) any_callback = any_callback || sr.prefiltered;
+            const std::function<void(int, float *)> prefilter = [&](int q, float * lg) {
+                FullJob & j = *ln.sjobs[(size_t) q];
+                const Decoder & d = *ln.sdecs[(size_t) q];
+                const SamplerRow & r = ln.srows[(size_t) q];
+                const Vocab & vc = ctx->model.vocab;
+                const int V = vc.n_vocab;
+                if (r.temperature > 0.0f)
+                    for (int k = 0; k < V; ++k) lg[k] /= r.temperature;
+                if (r.suppress_blank && r.is_initial) {
+                    lg[vc.token_eot] = -INFINITY;
+                    if (sst.token_space >= 0) lg[sst.token_space] = -INFINITY;
+                }
+                for (int k = 0; k < V; ++k)
+                    if (ctx->suppress_pre_host[(size_t) k]) lg[k] = -INFINITY;
+                if (r.no_timestamps)
+                    for (int k = vc.token_beg; k < V; ++k) lg[k] = -INFINITY;
+                j.params.logits_filter_callback(j.wctx(), j.wstate(), d.sequence.tokens.data(), (int) d.sequence.tokens.size(), lg,
+                                                j.params.logits_filter_callback_user_data);
+            };
             const int n_rows = (int) ln.rows.size();
             const int64_t tg1 = host_prof ? time_us() : 0;
-            const bool fused_step = step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
+            const bool fused_step = !any_callback && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
             const int64_t tg2 = host_prof ? time_us() : 0;
             hp_gather += tg1 - tg0;
             hp_elig += tg2 - tg1;
@@ -1076,7 +1104,7 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
                 }
             } else {
                 ok = stage_decode(*ctx, ln.rows.data(), n_rows, false) &&
-                     stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data());
+                     stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data(), any_callback ? &prefilter : nullptr);
             }
             if (!ok) {
                 log_error("%s: failed to decode\n", __func__);

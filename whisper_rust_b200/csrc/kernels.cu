@@ -693,11 +693,18 @@ sampler_kernel(SamplerStatic st, const float * __restrict__ logits_all, int64_t 
     // ---- filters (whisper.cpp:6183-6302)
     float mx = -INFINITY;
     for (int i = tid; i < V; i += SM_THREADS) {
-        float x = lin[i];
-        if (r.temperature > 0.0f) x = __fdiv_rn(x, r.temperature);
-        bool kill = st.suppress[i] != 0;
-        if (r.suppress_blank && r.is_initial && (i == st.token_eot || i == st.token_space)) kill = true;
-        if (r.no_timestamps && i >= beg) kill = true;
+        float x;
+        bool kill;
+        if (r.prefiltered) {
+            x = lg[i];
+            kill = st.suppress_post[i] != 0;
+        } else {
+            x = lin[i];
+            if (r.temperature > 0.0f) x = __fdiv_rn(x, r.temperature);
+            kill = st.suppress[i] != 0;
+            if (r.suppress_blank && r.is_initial && (i == st.token_eot || i == st.token_space)) kill = true;
+            if (r.no_timestamps && i >= beg) kill = true;
+        }
         if (r.last_was_ts) {
             if (r.penult_was_ts) kill = kill || (i >= beg);
             else kill = kill || (i < st.token_eot);

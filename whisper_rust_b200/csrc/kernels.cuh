@@ -84,6 +84,7 @@ bool cross_attn_decode(const __half * q, int ldq, const CrossKvRow * rows, int n
 // ------------------------------------------------------------------------------------------
 struct SamplerStatic {
     const uint8_t * suppress;  // [V] 1 = always -inf (not/sot/nosp/solm/translate/transcribe/prev/langs/nst/regex)
+    const uint8_t * suppress_post;  // [V] the subset applied after logits_filter_callback (regex, non-speech tokens; wc:6230-6262)
     int n_vocab, token_eot, token_beg, token_space, token_nosp;
 };
 struct SamplerRow {
@@ -95,6 +96,8 @@ struct SamplerRow {
     int   has_ts, tid0;    // monotone rule: suppress [beg, beg + tid0)
     int   want_nosp;       // also report softmax(raw logits)[nosp]
     int   work_slot;       // which [3][V] work area (logits, logprobs, probs) to use
+    int   prefiltered;     // 1: the work area already holds the logits after temperature, the static suppressions of wc:6187-6224 and
+                           // logits_filter_callback (done on the host); continue from the rules that follow the callback
 };
 struct SamplerOut {
     int   id, tid;
