@@ -40,7 +40,12 @@ __device__ __forceinline__ float fast_exp2(float x) {
 
 // kVRow = true : V in the same per-head [t][64] panels as Q and K (panel 2H + h): the P.V MMA reads it as an MN-major B operand
 // kVRow = false: V^T panels [H][W][64][Tpad] (K-major B operand)
-template <bool kVRow>
+// kOnePass = true : one pass over the K tiles with a running reference maximum per row.  p = exp2((s - m_run) * scale) where m_run
+//                   only moves when a tile's maximum exceeds it by more than 2^8 (then O and sum(p) of that row are rescaled in
+//                   TMEM by exp2(m_old - m_new)); softmax is shift-invariant, so O / sum(p) is the same quantity as with the exact
+//                   row maximum, P keeps f16's relative precision (p <= 256), and the second Q.K^T pass disappears.
+// kOnePass = false: the two-pass form described above (WB200_ATTN_TWOPASS=1).
+template <bool kVRow, bool kOnePass>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_constant__ CUtensorMap tmap_vt, __half * __restrict__ out,
                 int T, int R, int H, int W, int S, float scale_log2e) {
@@ -108,7 +113,8 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
                 tma_load_2d(k_smem + st * AT_TILE, &tmap_qk, k_full + st, 0, k_row + j * AT_KV);
                 ++kn;
             };
-            for (int j = 0; j < nkv; ++j) load_k(j);
+            if constexpr (!kOnePass)
+                for (int j = 0; j < nkv; ++j) load_k(j);
             for (int j = 0; j < nkv; ++j) {
                 load_k(j);
                 const int st = j % AT_NV;
@@ -146,8 +152,9 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
                 umma_commit(k_empty + st);
                 ++sn;
             };
-            for (int j = 0; j < nkv; ++j) issue_s();  // pass A
-            issue_s();                                // pass B, tile 0
+            if constexpr (!kOnePass)
+                for (int j = 0; j < nkv; ++j) issue_s();  // pass A
+            issue_s();                                    // pass B, tile 0
             for (int j = 0; j < nkv; ++j) {
                 if (j + 1 < nkv) issue_s();
                 const int st = j % AT_NV;
@@ -194,25 +201,59 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
 
         // pass A: row maximum over the valid kv columns
         float mx = -INFINITY;
-        for (int j = 0; j < nkv; ++j) {
-            load_s(j);
-            const int valid = T - j * AT_KV;  // columns >= valid are beyond this window
+        if constexpr (!kOnePass) {
+            for (int j = 0; j < nkv; ++j) {
+                load_s(j);
+                const int valid = T - j * AT_KV;  // columns >= valid are beyond this window
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
+                for (int c = 0; c < 4; ++c)
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+            }
         }
-        const float m_scaled = mx * scale_log2e;
+        float m_scaled = mx * scale_log2e;  // one-pass: the running reference maximum, set at tile 0
 
         // pass B: p = exp2(s * scale * log2e - m_scaled), P tile in shared memory, running sum
         float lsum = 0.0f;
         uint8_t * p_row = p_smem + (g * 2) * AT_TILE + row * 128;
         const uint32_t sw = (uint32_t) (row & 7);
         for (int j = 0; j < nkv; ++j) {
-            load_s(nkv + j);
+            load_s(kOnePass ? j : nkv + j);
             const int valid = T - j * AT_KV;
-            mbar_wait(p_empty + g, (j & 1) ^ 1);  // the P.V MMAs of tile j-1 have read this buffer
+            mbar_wait(p_empty + g, (j & 1) ^ 1);  // the P.V MMAs of tile j-1 have read this buffer (and O is quiescent)
+            if constexpr (kOnePass) {
+                float tm = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i < valid) tm = fmaxf(tm, __uint_as_float(r[c][i]));
+                const float tms = tm * scale_log2e;
+                if (j == 0) {
+                    m_scaled = tms;
+                } else {
+                    const bool grow = tms > m_scaled + 8.0f;
+                    if (__any_sync(0xffffffffu, grow)) {  // rare: the row's scale moves by more than 2^8
+                        const float m_new = grow ? tms : m_scaled;
+                        const float f = fast_exp2(m_scaled - m_new);  // exactly 1 for the rows that keep their reference
+                        m_scaled = m_new;
+                        lsum *= f;
+                        tc_fence_after();
+#pragma unroll 1
+                        for (int c0 = 0; c0 < 64; c0 += 16) {
+                            uint32_t o[16];
+                            tmem_ld_32x16(t_o + (uint32_t) c0, o);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+                            tmem_st_32x16(t_o + (uint32_t) c0, o);
+                        }
+                        tmem_st_wait();
+                        tc_fence_before();
+                    }
+                }
+            }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
 #pragma unroll
@@ -281,8 +322,10 @@ uint64_t enc_attn_launch_count() { return g_attn_launches.load(); }
 bool enc_attention(const __half * qk, const __half * vT, __half * out, int W, int T, int Tpad, int H, int S, float scale, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
-        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         attr_set = true;
     }
     const int R = W * T;
@@ -294,8 +337,15 @@ bool enc_attention(const __half * qk, const __half * vT, __half * out, int W, in
     dim3 grid(ceil_div(T, 256), H, W);
     const double flops = 4.0 * (double) T * T * 64 * H * W;
     ProfScope prof_scope(PC_ENC_SOFTMAX, stream, (double) R * S * 2 * 4, flops);
-    if (vrow) enc_attn_kernel<true><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, scale * 1.4426950408889634f);
-    else enc_attn_kernel<false><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, scale * 1.4426950408889634f);
+    static const bool two_pass = getenv("WB200_ATTN_TWOPASS") != nullptr;
+    const float sl2 = scale * 1.4426950408889634f;
+    if (two_pass) {
+        if (vrow) enc_attn_kernel<true, false><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, sl2);
+        else enc_attn_kernel<false, false><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, sl2);
+    } else {
+        if (vrow) enc_attn_kernel<true, true><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, sl2);
+        else enc_attn_kernel<false, true><<<grid, AT_THREADS, AT_SMEM, stream>>>(tq, tv, out, T, R, H, W, S, sl2);
+    }
     WB_CUDA_OK(cudaGetLastError());
     g_attn_launches.fetch_add(1);
     return true;
