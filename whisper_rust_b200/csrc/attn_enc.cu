@@ -199,17 +199,28 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
             if (lane == 0) mbar_arrive(s_empty + g);
         };
 
+        // columns beyond the window only exist in the last kv tile: they are set to -inf once there (exp2 -> 0, max unaffected), so the
+        // per-element work of every tile carries no bounds predicate
+        auto mask_tail = [&](int valid) {
+            if (valid < AT_KV) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i >= valid) r[c][i] = 0xff800000u;
+            }
+        };
+
         // pass A: row maximum over the valid kv columns
         float mx = -INFINITY;
         if constexpr (!kOnePass) {
             for (int j = 0; j < nkv; ++j) {
                 load_s(j);
-                const int valid = T - j * AT_KV;  // columns >= valid are beyond this window
+                mask_tail(T - j * AT_KV);  // columns >= valid are beyond this window
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
             }
         }
         float m_scaled = mx * scale_log2e;  // one-pass: the running reference maximum, set at tile 0
@@ -220,15 +231,14 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
         const uint32_t sw = (uint32_t) (row & 7);
         for (int j = 0; j < nkv; ++j) {
             load_s(kOnePass ? j : nkv + j);
-            const int valid = T - j * AT_KV;
+            mask_tail(T - j * AT_KV);
             mbar_wait(p_empty + g, (j & 1) ^ 1);  // the P.V MMAs of tile j-1 have read this buffer (and O is quiescent)
             if constexpr (kOnePass) {
                 float tm = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (c * 32 + i < valid) tm = fmaxf(tm, __uint_as_float(r[c][i]));
+                    for (int i = 0; i < 32; ++i) tm = fmaxf(tm, __uint_as_float(r[c][i]));
                 const float tms = tm * scale_log2e;
                 if (j == 0) {
                     m_scaled = tms;
@@ -261,8 +271,7 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
                     float pv[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        float p = fast_exp2(fmaf(__uint_as_float(r[c][q * 8 + i]), scale_log2e, -m_scaled));
-                        if (c * 32 + q * 8 + i >= valid) p = 0.0f;
+                        const float p = fast_exp2(fmaf(__uint_as_float(r[c][q * 8 + i]), scale_log2e, -m_scaled));
                         lsum += p;
                         pv[i] = p;
                     }
