@@ -234,11 +234,12 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
             mask_tail(T - j * AT_KV);
             mbar_wait(p_empty + g, (j & 1) ^ 1);  // the P.V MMAs of tile j-1 have read this buffer (and O is quiescent)
             if constexpr (kOnePass) {
-                float tm = -INFINITY;
+                float tm4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four independent chains: the compare latency overlaps
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) tm = fmaxf(tm, __uint_as_float(r[c][i]));
+                    for (int i = 0; i < 32; ++i) tm4[i & 3] = fmaxf(tm4[i & 3], __uint_as_float(r[c][i]));
+                const float tm = fmaxf(fmaxf(tm4[0], tm4[1]), fmaxf(tm4[2], tm4[3]));
                 const float tms = tm * scale_log2e;
                 if (j == 0) {
                     m_scaled = tms;
@@ -272,7 +273,7 @@ enc_attn_kernel(const __grid_constant__ CUtensorMap tmap_qk, const __grid_consta
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         const float p = fast_exp2(fmaf(__uint_as_float(r[c][q * 8 + i]), scale_log2e, -m_scaled));
-                        lsum += p;
+                        lsum += p;  // one chain, in column order: the sum's rounding is part of the pinned numerics (goldens)
                         pv[i] = p;
                     }
                     uint4 pk;
