@@ -318,7 +318,24 @@ bool softmax_rows_f16(const float * s, int64_t rows, int n, int64_t lds, float s
 // The fc1 GEMM stores h = f16(W1.x + b1) - the value the reference's lookup is indexed by - and this pass maps h -> table[h].
 // The table sits in shared memory (128 KB): a warp's 32 random lookups cost ~3-4 bank cycles instead of up to 32 L1 wavefronts.
 // =============================================================================================
-__global__ void __launch_bounds__(512, 1)
+__device__ __forceinline__ uint4 gelu_lookup8(uint4 v, const uint16_t * tab) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        uint32_t lo = w[k] & 0xffffu, hi = w[k] >> 16;
+        // x <= -10 -> 0, x >= 10 -> x (vec.h:575-580); f16 bit patterns: 10.0 = 0x4900, -10.0 = 0xC900
+        const uint32_t alo = lo & 0x7fffu, ahi = hi & 0x7fffu;
+        uint32_t rlo = tab[lo], rhi = tab[hi];
+        if (alo >= 0x4900u && alo <= 0x7c00u) rlo = (lo & 0x8000u) ? 0u : lo;
+        if (ahi >= 0x4900u && ahi <= 0x7c00u) rhi = (hi & 0x8000u) ? 0u : hi;
+        w[k] = rlo | (rhi << 16);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// One persistent CTA per SM (the table takes 128 KB of its shared memory); 1024 threads x 4 independent 16-byte loads keep
+// 64 KB per SM in flight, which is what an HBM-bound pass needs on this part.
+__global__ void __launch_bounds__(1024, 1)
 gelu_table_kernel(__half * __restrict__ x, int64_t n8 /* groups of 8 halves */, const __half * __restrict__ table) {
     extern __shared__ uint4 gelu_tab_raw[];
     uint16_t * tab = (uint16_t *) gelu_tab_raw;
@@ -326,21 +343,16 @@ gelu_table_kernel(__half * __restrict__ x, int64_t n8 /* groups of 8 halves */, 
     for (int i = threadIdx.x; i < 65536 * 2 / 16; i += blockDim.x) gelu_tab_raw[i] = __ldg(tsrc + i);
     __syncthreads();
     uint4 * xv = (uint4 *) x;
-    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t) gridDim.x * blockDim.x) {
-        uint4 v = xv[i];
-        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n8; i += 4 * stride) {
+        uint4 v[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            uint32_t lo = w[k] & 0xffffu, hi = w[k] >> 16;
-            // x <= -10 -> 0, x >= 10 -> x (vec.h:575-580); f16 bit patterns: 10.0 = 0x4900, -10.0 = 0xC900
-            const uint32_t alo = lo & 0x7fffu, ahi = hi & 0x7fffu;
-            uint32_t rlo = tab[lo], rhi = tab[hi];
-            if (alo >= 0x4900u && alo <= 0x7c00u) rlo = (lo & 0x8000u) ? 0u : lo;
-            if (ahi >= 0x4900u && ahi <= 0x7c00u) rhi = (hi & 0x8000u) ? 0u : hi;
-            w[k] = rlo | (rhi << 16);
-        }
-        xv[i] = make_uint4(w[0], w[1], w[2], w[3]);
+        for (int u = 0; u < 4; ++u) v[u] = xv[i + u * stride];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) xv[i + u * stride] = gelu_lookup8(v[u], tab);
     }
+    for (; i < n8; i += stride) xv[i] = gelu_lookup8(xv[i], tab);
 }
 
 bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_t stream) {
@@ -352,9 +364,9 @@ bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_
     WB_CHECK(n % 8 == 0 && ((uintptr_t) x & 15) == 0, "gelu_table_inplace: %lld elements must be a multiple of 8, 16-byte aligned\n", (long long) n);
     ProfScope prof_scope(PC_OTHER, stream, (double) n * 4);
     const int64_t n8 = n / 8;
-    const int grid = (int) std::min<int64_t>(ceil_div64(n8, 512), 148 * 2);
+    const int grid = (int) std::min<int64_t>(ceil_div64(n8, 1024), 148);
     if (grid <= 0) return true;
-    gelu_table_kernel<<<grid, 512, 65536 * 2, stream>>>(x, n8, table);
+    gelu_table_kernel<<<grid, 1024, 65536 * 2, stream>>>(x, n8, table);
     WB_LAUNCHED();
     return true;
 }
