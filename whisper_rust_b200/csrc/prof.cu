@@ -7,7 +7,8 @@ namespace wb {
 
 static const char * k_names[PC_COUNT] = {"mel", "gemm_encoder", "encoder_softmax", "layernorm", "gemm_decoder", "gemm_logits",
                                          "self_attn_decode", "cross_attn_decode", "sampler", "embed", "dtw", "other", "layernorm_decode",
-                                         "event_bracket_null_kernel"};
+                                         "event_bracket_null_kernel", "cross_attn_step", "gemm_step_qkv", "gemm_step_attn_proj",
+                                         "gemm_step_fc1", "gemm_step_fc2"};
 const char * prof_cat_name(int cat) { return cat >= 0 && cat < PC_COUNT ? k_names[cat] : "?"; }
 
 int g_prof_gemm_cat = PC_OTHER;

@@ -9,7 +9,8 @@ namespace wb {
 
 enum ProfCat : int {
     PC_MEL = 0, PC_GEMM_ENC, PC_ENC_SOFTMAX, PC_LN, PC_GEMM_DEC, PC_GEMM_LOGITS, PC_SELF_ATTN, PC_CROSS_ATTN, PC_SAMPLER, PC_EMBED,
-    PC_DTW, PC_OTHER, PC_LN_DEC, PC_CALIB, PC_COUNT
+    PC_DTW, PC_OTHER, PC_LN_DEC, PC_CALIB, PC_CROSS_STEP, PC_GEMM_STEP_QKV, PC_GEMM_STEP_SQ,
+    PC_GEMM_STEP_FC1, PC_GEMM_STEP_FC2, PC_COUNT
 };
 const char * prof_cat_name(int cat);
 

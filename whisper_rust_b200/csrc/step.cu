@@ -571,7 +571,9 @@ static bool gemm_wcluster(const __half * W, const __half * X, int n, int N_out, 
     a.mode = o.mode; a.out = o.out; a.ldo = o.ldo; a.bias = o.bias; a.scale = o.scale; a.scale_f1 = o.scale_f1;
     a.gelu_table = o.gelu_table; a.tmem_cols = p.tmem_cols; a.tok_per_rank = p.tok_per_rank;
     a.trace = trace_slot(N_out == 3 * K ? "gemm_qkv" : N_out == 4 * K ? "gemm_fc1" : K == 4 * N_out ? "gemm_fc2" : "gemm_sq");
-    ProfScope prof_scope(PC_GEMM_DEC, s, (double) N_out * K * 2 + (double) n * K * 2);
+    // one profiler category per launch shape of the step (they are separate lines of the ncu launch list too)
+    ProfScope prof_scope(N_out == 3 * K ? PC_GEMM_STEP_QKV : N_out == 4 * K ? PC_GEMM_STEP_FC1 : K == 4 * N_out ? PC_GEMM_STEP_FC2 : PC_GEMM_STEP_SQ, s,
+                         (double) N_out * K * 2 + (double) n * K * 2);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.split, p.tiles);
     cfg.blockDim = dim3(WS_THREADS);
@@ -1095,7 +1097,7 @@ static bool launch_cross(CrossArgs a, int n_rows, cudaStream_t s, bool pdl) {
     a.stages = std::max(2, std::min(g_tune.xs_stages, 8));
     const int grid = std::min(a.items, step_sm_count() * std::max(1, g_tune.xs_ctas_per_sm));
     // algorithmic bytes: the K and V panels of every (row, head), f16
-    ProfScope prof_scope(PC_CROSS_ATTN, s, (double) a.items * a.T * 64 * 2 * 2, (double) a.items * a.T * 64 * 4);
+    ProfScope prof_scope(PC_CROSS_STEP, s, (double) a.items * a.T * 64 * 2 * 2, (double) a.items * a.T * 64 * 4);
     return launch_k(cross_attn_step_kernel, dim3(grid), dim3(XS_THREADS), (size_t) xs_smem_bytes(a.T, a.stages), s, pdl, a);
 }
 
