@@ -940,7 +940,8 @@ int full_with_states(Context * ctx, State * const * states, int n_states, const 
     {
         const char * e = getenv("WB200_LANES");
         if (e && atoi(e) > 0) n_lanes = atoi(e);
-        else n_lanes = std::min(4, n_states / 64);  // measured on B200: 4 lanes of 64 rows beat 1 x 256 by ~5 %
+        else n_lanes = std::max(std::min(4, n_states / 64), (n_states + 255) / 256);  // measured on B200: 4 lanes of 64-96 rows
+                                                                                      // beat one of 256 by ~5 %; a lane's fused step takes at most 256 rows
         n_lanes = std::max(1, std::min(n_lanes, std::min(n_states, step_max_lanes())));
     }
     std::vector<Lane> lanes((size_t) n_lanes);
