@@ -1135,6 +1135,7 @@ struct StepWs {
     std::vector<int> trace_subs;
     int trace_n = 0;                         // rows of the traced step
     int kv_cells_max = 0;                    // largest self-KV cache (cells) among the staged rows: sizes self_attn_step's score buffer
+    int64_t kv_cells_live = 0;               // live cells summed over the staged rows (algorithmic bytes of self_attn_step)
 };
 
 struct StageLayout {
@@ -1278,7 +1279,7 @@ struct LaneIssue {
             SelfArgs a{};
             a.qkv16 = ws.qkv16; a.rows = d_self; a.S = S; a.layer = il; a.out = ws.att;
             a.trace = trace_slot("self");
-            ProfScope prof_scope(PC_SELF_ATTN, s);
+            ProfScope prof_scope(PC_SELF_ATTN, s, (double) ws.kv_cells_live * S * 2 * 2 /* K and V rows of every live cell, f16 */);
             // the score buffer only has to hold the cache's cells (step_eligible bounds them by 5000): 2 KB instead of 20 KB for
             // the greedy cache of 512 cells, which lifts the kernel from 9 to 16 resident CTAs per SM
             const size_t sc_bytes = (size_t) std::min(5120, std::max(256, (int) pad_to(ws.kv_cells_max, 64))) * 4;
@@ -1499,6 +1500,7 @@ static bool fill_stage(StepWs & ws, const BatchRow * rows, const SamplerRow * sr
     CrossKvRow * h_cross = (CrossKvRow *) (ws.h_stage + SL.o_cross);
     SamplerRow * h_samp = (SamplerRow *) (ws.h_stage + SL.o_samp);
     ws.kv_cells_max = 0;
+    ws.kv_cells_live = 0;
     for (int i = 0; i < n; ++i) {
         State * st = rows[i].st;
         KvCache & kv = st->kv_self;
@@ -1513,6 +1515,7 @@ static bool fill_stage(StepWs & ws, const BatchRow * rows, const SamplerRow * sr
         sr.k_base = kv.k; sr.v_base = kv.v; sr.cells = nullptr;
         sr.n_cells = kv.head + 1; sr.store_cell = kv.head; sr.n_ctx = kv.size;
         ws.kv_cells_max = std::max(ws.kv_cells_max, kv.size);
+        ws.kv_cells_live += kv.head + 1;
         h_cross[i] = CrossKvRow{st->kv_cross, nullptr, 0, 0};
         h_samp[i] = srows[i];
         h_samp[i].logits_row = i;
