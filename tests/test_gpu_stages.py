@@ -201,3 +201,24 @@ def test_logits_filter_callback_matches_oracle(prod_lib, ref_lib):
     assert out["ref"][1] == out["b200"][1] and len(out["ref"][1]) > 10
     ids = [t["id"] for s in out["b200"][0] for t in s.tokens]
     assert any(1000 <= i < 1300 for i in ids) and not any(2000 <= i < 2064 for i in ids)
+
+
+@pytest.mark.parametrize("seconds,seed,max_len,split_on_word", [(30.0, 26, 0, False), (30.0, 26, 12, False), (47.3, 26, 20, True),
+                                                                (11.0, 3, 1, False)])
+def test_heuristic_token_timestamps_and_wrapping_match_oracle(prod_lib, ref_lib, seconds, seed, max_len, split_on_word):
+    """`token_timestamps = true` (whisper_exp_compute_token_level_timestamps, wc:8390-8615: anchors from the timestamp-token
+    statistics, voice-length split, signal-energy edges) and `max_len` / `split_on_word` (whisper_wrap_segment, wc:6049-6100):
+    integer token times, voice lengths and the wrapped segments must be identical to the reference's."""
+    pcm = synth.synth_audio(seconds, seed=seed)
+    out = {}
+    for name, lib, gpu in (("ref", ref_lib, False), ("b200", prod_lib, True)):
+        ctx = WhisperContext.new_from_buffer_with_params(model_blob("mini", RICH), WhisperContextParameters(use_gpu=gpu), lib=lib)
+        st = ctx.create_state()
+        p = FullParams(lib, SamplingStrategy.GREEDY, best_of=1)
+        p.set_n_threads(8).set_language("en").set_temperature_inc(0.0)
+        p.set_token_timestamps(True).set_max_len(max_len).set_split_on_word(split_on_word)
+        assert st.full(p, pcm) == 0
+        out[name] = [(s.t0, s.t1, s.text, [(t["id"], t["t0"], t["t1"], t["vlen"]) for t in s.tokens]) for s in st.segments()]
+        st.free(); ctx.free()
+    assert len(out["ref"]) > 0 and any(t[1] >= 0 for s in out["ref"] for t in s[3])
+    assert out["b200"] == out["ref"]

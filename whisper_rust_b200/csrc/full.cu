@@ -183,6 +183,10 @@ static const char * token_str(const Vocab & vc, int id) {
     return vc.id_to_token[(size_t) id].c_str();
 }
 
+// F5 (defined below): heuristic token times of one segment, wrapping of the newest segment
+static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment, float thold_pt, float thold_ptsum);
+static int wrap_last_segment(Context * ctx, State * st, int max_len, bool split_on_word);
+
 // --------------------------------------------------------------------------------------------
 // the per-state job
 // --------------------------------------------------------------------------------------------
@@ -271,10 +275,26 @@ bool FullJob::init() {
             return false;
         }
     }
-    if (params.token_timestamps) {
+    if (params.token_timestamps) {  // wc:6832-6839
         st->t_beg = 0;
         st->t_last = 0;
         st->tid_last = 0;
+        if (n_samples > 0) {
+            // moving average of |pcm| over 65 samples, computed on the device copy of the PCM (the caller's pointer may be device
+            // memory in the batch entry point) and brought to the host, where the heuristic's scalar walks run
+            float * d_energy = nullptr;
+            st->energy.assign((size_t) n_samples, 0.0f);
+            const bool ok = cudaMalloc((void **) &d_energy, (size_t) n_samples * sizeof(float)) == cudaSuccess &&
+                            signal_energy(st->d_pcm, n_samples, 32, d_energy, ctx->stream) &&
+                            cudaMemcpyAsync(st->energy.data(), d_energy, (size_t) n_samples * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess &&
+                            cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+            cudaFree(d_energy);
+            if (!ok) {
+                log_error("%s: failed to compute the signal energy\n", __func__);
+                finish(-2);
+                return false;
+            }
+        }
     }
     seek_start = params.offset_ms / 10;
     seek_end = params.duration_ms == 0 ? st->n_len_org : seek_start + params.duration_ms / 10;
@@ -785,6 +805,12 @@ void FullJob::emit_results() {
     if (prompt.front() == vc.token_prev) prompt_past.insert(prompt_past.end(), prompt.begin() + 1, prompt.end() - (long) prompt_init.size());
     for (int k = 0; k < result_len && !is_no_speech; ++k) prompt_past.push_back(tokens_cur[(size_t) k].id);
 
+    // wc:7619-7626 / 7664-7671: heuristic token times for the segment just pushed, then optional wrapping; returns n_new
+    auto token_times = [&]() {
+        if (!params.token_timestamps) return 1;
+        heuristic_token_timestamps(ctx, st, (int) result_all.size() - 1, params.thold_pt, params.thold_ptsum);
+        return params.max_len > 0 ? wrap_last_segment(ctx, st, params.max_len, params.split_on_word) : 1;
+    };
     auto notify = [&](int n_new) {
         if (params.new_segment_callback && !ctx->params.dtw_token_timestamps)
             params.new_segment_callback(wctx(), wstate(), n_new, params.new_segment_callback_user_data);
@@ -807,7 +833,7 @@ void FullJob::emit_results() {
                     }
                     result_all.push_back({t0, t1, text, st->no_speech_prob, {}, speaker_turn_next});
                     for (int j = i0; j <= k; j++) result_all.back().tokens.push_back(tokens_cur[(size_t) j]);
-                    notify(1);
+                    notify(token_times());
                 }
                 text = "";
                 while (k < (int) tokens_cur.size() && tokens_cur[(size_t) k].id > vc.token_beg) k++;
@@ -825,7 +851,7 @@ void FullJob::emit_results() {
             }
             result_all.push_back({t0, t1, text, st->no_speech_prob, {}, speaker_turn_next});
             for (int j = i0; j < (int) tokens_cur.size(); j++) result_all.back().tokens.push_back(tokens_cur[(size_t) j]);
-            notify(1);
+            notify(token_times());
         }
     }
     {   // DTW (wc:7680-7692)
@@ -844,6 +870,178 @@ void FullJob::emit_results() {
     if (single_timestamp_ending) seek_delta = std::min(seek_end - seek, WHISPER_CHUNK_SIZE * 100);
     seek += seek_delta;
     phase = WINDOW_BEGIN;
+}
+
+// --------------------------------------------------------------------------------------------
+// F5: heuristic token timestamps (`token_timestamps = true`; wc:8335-8615) and segment wrapping (`max_len`; wc:6049-6100)
+// --------------------------------------------------------------------------------------------
+// Anchors: a token whose timestamp-token statistics are confident (pt, ptsum above the thresholds, tid advancing) pins the
+// boundary between itself and its predecessor at t_beg + 2 (tid - beg).  Runs of tokens between anchors share their span in
+// proportion to a "voice length" of their text; finally every text token's edges are pulled to where the moving average of
+// |signal| crosses half of its local mean.  Host arithmetic in the reference's types (int64 times, double split, f32 energy).
+static float text_voice_length(const char * text) {  // wc:8335-8357
+    float len = 0.0f;
+    for (const char * c = text; *c; ++c) {
+        if (*c == ' ') len += 0.01f;
+        else if (*c == ',') len += 2.00f;
+        else if (*c == '.' || *c == '!' || *c == '?' || (*c >= '0' && *c <= '9')) len += 3.00f;
+        else len += 1.00f;
+    }
+    return len;
+}
+
+static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment, float thold_pt, float thold_ptsum) {
+    const Vocab & vc = ctx->model.vocab;
+    Segment & seg = st->result_all[(size_t) i_segment];
+    auto & tk = seg.tokens;
+    const int n_samples = (int) st->energy.size(), n = (int) tk.size();
+    if (n_samples == 0) {
+        log_error("%s: no signal data available\n", __func__);
+        return;
+    }
+    if (n == 0) return;
+    const int64_t seg_t0 = seg.t0, seg_t1 = seg.t1;
+    if (n == 1) {
+        tk[0].t0 = seg_t0;
+        tk[0].t1 = seg_t1;
+        return;
+    }
+    // ---- anchors (wc:8432-8468); t_beg / t_last / tid_last persist across the segments of a call
+    for (int j = 0; j < n; ++j) {
+        whisper_token_data & t = tk[(size_t) j];
+        if (j == 0) {
+            if (t.id == vc.token_beg) {
+                t.t0 = seg_t0;
+                t.t1 = seg_t0;
+                tk[1].t0 = seg_t0;
+                st->t_beg = seg_t0;
+                st->t_last = seg_t0;
+                st->tid_last = vc.token_beg;
+            } else {
+                t.t0 = st->t_last;
+            }
+        }
+        const int64_t tt = st->t_beg + 2 * (int64_t) (t.tid - vc.token_beg);
+        t.vlen = text_voice_length(token_str(vc, t.id));
+        if (t.pt > thold_pt && t.ptsum > thold_ptsum && t.tid > st->tid_last && tt <= seg_t1) {
+            if (j > 0) tk[(size_t) j - 1].t1 = tt;
+            t.t0 = tt;
+            st->tid_last = t.tid;
+        }
+    }
+    tk[(size_t) n - 2].t1 = seg_t1;
+    tk[(size_t) n - 1].t0 = seg_t1;
+    tk[(size_t) n - 1].t1 = seg_t1;
+    st->t_last = seg_t1;
+
+    // ---- runs without a known end share [first.t0, last.t1] in proportion to the voice lengths (wc:8472-8510)
+    for (int first = 0; first < n;) {
+        int last = first;
+        while (last < n && tk[(size_t) last].t1 < 0) ++last;
+        if (last >= n) last = n - 1;
+        if (last > first) {
+            double total = 0.0;
+            for (int j = first; j <= last; ++j) total += tk[(size_t) j].vlen;
+            const double span = (double) (tk[(size_t) last].t1 - tk[(size_t) first].t0);
+            for (int j = first + 1; j <= last; ++j) {
+                const double cut = tk[(size_t) j - 1].t0 + span * tk[(size_t) j - 1].vlen / total;
+                tk[(size_t) j - 1].t1 = (int64_t) cut;
+                tk[(size_t) j].t0 = (int64_t) cut;
+            }
+        }
+        first = last + 1;
+    }
+    // ---- consistency pass (wc:8513-8525)
+    for (int j = 0; j < n - 1; ++j) {
+        if (tk[(size_t) j].t1 < 0) tk[(size_t) j + 1].t0 = tk[(size_t) j].t1;
+        if (j > 0 && tk[(size_t) j - 1].t1 > tk[(size_t) j].t0) {
+            tk[(size_t) j].t0 = tk[(size_t) j - 1].t1;
+            tk[(size_t) j].t1 = std::max(tk[(size_t) j].t0, tk[(size_t) j].t1);
+        }
+    }
+    // ---- energy edges (wc:8529-8593).  Times map to samples RELATIVE to the segment start, as in the reference
+    const std::vector<float> & en = st->energy;
+    auto to_sample = [&](int64_t t) {
+        const int sidx = (int) (((t - seg_t0) * WHISPER_SAMPLE_RATE) / 100);
+        return std::max(0, std::min(n_samples - 1, sidx));
+    };
+    auto to_time = [&](int sidx) { return (100ll * sidx) / WHISPER_SAMPLE_RATE + seg_t0; };
+    const int reach = WHISPER_SAMPLE_RATE / 8;
+    for (int j = 0; j < n; ++j) {
+        whisper_token_data & t = tk[(size_t) j];
+        if (t.id >= vc.token_eot) continue;
+        int s_lo = to_sample(t.t0), s_hi = to_sample(t.t1);
+        const int w_lo = std::max(s_lo - reach, 0), w_hi = std::min(s_hi + reach, n_samples);
+        float acc = 0.0f;
+        for (int k = w_lo; k < w_hi; ++k) acc += en[(size_t) k];
+        const float level = (float) (0.5 * acc / (w_hi - w_lo));
+        {   // leading edge: walk out while loud (but not into the previous token), else walk in to the first loud sample
+            int k = s_lo;
+            if (en[(size_t) k] > level && j > 0) {
+                while (k > 0 && en[(size_t) k] > level) --k;
+                t.t0 = to_time(k);
+                if (t.t0 < tk[(size_t) j - 1].t1) t.t0 = tk[(size_t) j - 1].t1;
+                else s_lo = k;
+            } else {
+                while (en[(size_t) k] < level && k < s_hi) ++k;
+                s_lo = k;
+                t.t0 = to_time(k);
+            }
+        }
+        {   // trailing edge, mirrored
+            int k = s_hi;
+            if (en[(size_t) k] > level) {
+                while (k < n_samples - 1 && en[(size_t) k] > level) ++k;
+                t.t1 = to_time(k);
+                if (j < n - 1 && t.t1 > tk[(size_t) j + 1].t0) t.t1 = tk[(size_t) j + 1].t0;
+                else s_hi = k;
+            } else {
+                while (en[(size_t) k] < level && k > s_lo) --k;
+                s_hi = k;
+                t.t1 = to_time(k);
+            }
+        }
+    }
+}
+
+// Splits the newest segment so that no piece's text exceeds max_len bytes (optionally only at tokens that start a word);
+// pieces take over the token times computed above.  Returns the number of segments the newest one became.
+static int wrap_last_segment(Context * ctx, State * st, int max_len, bool split_on_word) {
+    const Vocab & vc = ctx->model.vocab;
+    auto & all = st->result_all;
+    Segment cur = all.back();  // the piece being scanned (a copy: `all` grows underneath)
+    int pieces = 1, used = 0;
+    std::string text;
+    for (int i = 0; i < (int) cur.tokens.size(); ++i) {
+        const whisper_token_data & t = cur.tokens[(size_t) i];
+        if (t.id >= vc.token_eot) continue;
+        const char * txt = token_str(vc, t.id);
+        const int len = (int) strlen(txt);
+        const bool may_split = !split_on_word || txt[0] == ' ';
+        if (used + len > max_len && i > 0 && may_split) {
+            Segment & head = all.back();
+            head.text = std::move(text);
+            head.t1 = t.t0;
+            head.tokens.resize((size_t) i);
+            head.speaker_turn_next = false;
+            Segment tail{};
+            tail.t0 = t.t0;
+            tail.t1 = cur.t1;
+            tail.tokens.assign(cur.tokens.begin() + i, cur.tokens.end());
+            tail.speaker_turn_next = cur.speaker_turn_next;
+            all.push_back(tail);
+            used = 0;
+            text.clear();
+            cur = all.back();
+            i = -1;
+            ++pieces;
+        } else {
+            used += len;
+            text += txt;
+        }
+    }
+    all.back().text = std::move(text);
+    return pieces;
 }
 
 // --------------------------------------------------------------------------------------------

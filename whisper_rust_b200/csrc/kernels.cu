@@ -372,6 +372,28 @@ bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_
 }
 
 // =============================================================================================
+// F5: moving average of |x| (whisper.cpp:8360-8376), one thread per sample, the reference's summation order
+// =============================================================================================
+__global__ void signal_energy_kernel(const float * __restrict__ pcm, int n, int hw, float * __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float sum = 0.0f;
+    for (int j = -hw; j <= hw; ++j) {
+        const int k = i + j;
+        if (k >= 0 && k < n) sum = __fadd_rn(sum, fabsf(pcm[k]));
+    }
+    out[i] = __fdiv_rn(sum, (float) (2 * hw + 1));
+}
+
+bool signal_energy(const float * pcm, int n_samples, int half_window, float * out, cudaStream_t stream) {
+    if (n_samples <= 0) return true;
+    ProfScope prof_scope(PC_OTHER, stream, (double) n_samples * 8);
+    signal_energy_kernel<<<ceil_div(n_samples, 256), 256, 0, stream>>>(pcm, n_samples, half_window, out);
+    WB_LAUNCHED();
+    return true;
+}
+
+// =============================================================================================
 // decoder step: embedding
 // =============================================================================================
 __global__ void embed_kernel(const __half * __restrict__ te, const float * __restrict__ pe, const int * __restrict__ tokens,

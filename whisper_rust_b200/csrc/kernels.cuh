@@ -109,6 +109,12 @@ bool sample_rows(const SamplerStatic & st, const float * logits, int64_t ld_logi
                  SamplerOut * out, cudaStream_t stream);
 
 // ------------------------------------------------------------------------------------------
+// F5: signal energy for the token-timestamp heuristic (get_signal_energy, whisper.cpp:8360-8376)
+// ------------------------------------------------------------------------------------------
+// out[i] = (sum over j in [-hw, hw] of |pcm[i+j]|, samples outside the signal skipped, added in ascending j) / (2 hw + 1); f32 like the reference
+bool signal_energy(const float * pcm, int n_samples, int half_window, float * out, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------
 // X1/X2: DTW token timestamps  (whisper.cpp:8647-8933)
 // ------------------------------------------------------------------------------------------
 // qk: f32 [n_heads][n_tok][T] softmax rows; uses the first n_audio columns.
