@@ -330,13 +330,12 @@ uint64_t enc_attn_launch_count() { return g_attn_launches.load(); }
 // qk: f16 per-head panels [2H][R][64] (Q heads then K heads, R = W*T rows) followed, when vT == nullptr, by the V heads
 // ([3H][R][64]); otherwise vT: f16 [H][W][64][Tpad]; out: f16 [R][S]
 bool enc_attention(const __half * qk, const __half * vT, __half * out, int W, int T, int Tpad, int H, int S, float scale, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         WB_CUDA_OK(cudaFuncSetAttribute(enc_attn_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
-        attr_set = true;
     }
     const int R = W * T;
     const bool vrow = vT == nullptr;

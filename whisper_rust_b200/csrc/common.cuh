@@ -158,6 +158,20 @@ template <int N> __device__ __forceinline__ void bulk_wait_group() { asm volatil
 // named barrier over a subset of the CTA's warps (id 1..15; id 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(int id, int n_threads) { asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(n_threads) : "memory"); }
 // programmatic dependent launch (PDL): let the next kernel of the stream start its prologue / wait for the previous one
+// cudaFuncSetAttribute applies to the current device only: one flag per call site AND device, so that contexts on several
+// GPUs of one process (the crate allows it: gpu_device in whisper_context_params) each opt their kernels in.
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool first() {
+        int d = 0;
+        cudaGetDevice(&d);
+        d &= 63;
+        if (done[d]) return false;
+        done[d] = true;
+        return true;
+    }
+};
+
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
 

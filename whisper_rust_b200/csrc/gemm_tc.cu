@@ -554,11 +554,10 @@ uint64_t gemm_launch_count() { return g_gemm_launches.load(); }
 template <int BN>
 static bool launch_gemm(const CUtensorMap & ta, const CUtensorMap & tb, int M, int N, int K, int batch, int a_bcast, int b_bcast,
                         const GemmTaps & taps, const GemmEpilogue & epi, cudaStream_t stream) {
-    static bool attr_set = false;
+    static PerDeviceOnce attr_set;
     constexpr int smem = gemm_smem_bytes(BN);
-    if (!attr_set) {
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(gemm_f16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
     }
     dim3 grid(ceil_div(N, BN), ceil_div(M, BLOCK_M), batch);
     ProfScope prof_scope(g_prof_gemm_cat, stream,
@@ -642,11 +641,10 @@ static bool persist_eligible(const GemmEpilogue & e, const GemmTaps & taps, int 
 template <int BN, bool F16>
 static bool launch_gemm_persist(const CUtensorMap & ta, const CUtensorMap & tb, const CUtensorMap & tc, int M, int N, int K, int batch,
                                 int a_bcast, int b_bcast, const GemmEpilogue & e, cudaStream_t stream) {
-    static bool attr_set = false;
+    static PerDeviceOnce attr_set;
     constexpr int smem = pgemm_smem_bytes(BN);
-    if (!attr_set) {
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(gemm_f16_persist_kernel<BN, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
     }
     PersistEpi pe{};
     pe.bias = e.bias; pe.bias_batch_stride = e.bias_batch_stride;

@@ -356,10 +356,9 @@ gelu_table_kernel(__half * __restrict__ x, int64_t n8 /* groups of 8 halves */, 
 }
 
 bool gelu_table_inplace(__half * x, int64_t n, const __half * table, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(gelu_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536 * 2));
-        attr_set = true;
     }
     WB_CHECK(n % 8 == 0 && ((uintptr_t) x & 15) == 0, "gelu_table_inplace: %lld elements must be a multiple of 8, 16-byte aligned\n", (long long) n);
     ProfScope prof_scope(PC_OTHER, stream, (double) n * 4);

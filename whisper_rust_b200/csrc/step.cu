@@ -401,17 +401,18 @@ gemm_wcluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
 
 // ---- host side: plan (split / stages) and launch --------------------------------------------------------------
 static std::atomic<uint64_t> g_step_launches{0};
-static bool g_pdl = true;  // launch with programmatic stream serialization (WB200_NO_PDL=1 switches it off)
+// per-call launch settings: thread_local, because contexts on different GPUs may be driven from different host threads
+static thread_local bool g_pdl = true;  // launch with programmatic stream serialization (WB200_NO_PDL=1 switches it off)
 static int env_int(const char * name, int dflt) {
     const char * e = getenv(name);
     return e && *e ? atoi(e) : dflt;
 }
-static int g_launch_prio = 0;
+static thread_local int g_launch_prio = 0;
 // timeline capture (WB200_STEP_TRACE): next free stamp slot and the label of every slot handed out
-static unsigned long long * g_trace_next = nullptr;
-static std::vector<const char *> * g_trace_names = nullptr;
-static std::vector<int> * g_trace_subs = nullptr;
-static int g_trace_sub = 0;  // which half of a paired step the next launches belong to
+static thread_local unsigned long long * g_trace_next = nullptr;
+static thread_local std::vector<const char *> * g_trace_names = nullptr;
+static thread_local std::vector<int> * g_trace_subs = nullptr;
+static thread_local int g_trace_sub = 0;  // which half of a paired step the next launches belong to
 static unsigned long long * trace_slot(const char * name) {
     if (!g_trace_next) return nullptr;
     if (g_trace_names) g_trace_names->push_back(name);
@@ -424,7 +425,7 @@ static unsigned long long * trace_slot(const char * name) {
 struct LaneTuning {
     int xs_ctas_per_sm = 2, xs_stages = 5, wc_smem_cap = 192 * 1024;
 };
-static LaneTuning g_tune;
+static thread_local LaneTuning g_tune;
 
 struct WsPlan {
     int tiles, split, kb_total, kb_per_split, stages, n_pad, smem;
@@ -497,10 +498,9 @@ static bool gemm_wstream(const __half * W, const __half * X, int n, int N_out, i
     WB_CHECK(n >= 1 && n <= 256, "gemm_wstream handles 1..256 token rows (got %d)\n", n);
     const bool direct = o.out != nullptr;
     WsPlan p = ws_plan(n, N_out, K, direct ? 1 : force_split);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(gemm_wstream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-        attr_set = true;
     }
     CUtensorMap tw, tx;
     if (!tmap_encode_2d(&tw, W, (uint64_t) K, (uint64_t) N_out, (uint64_t) K, 64, 128)) return false;
@@ -556,10 +556,9 @@ struct WcOut {
 static bool gemm_wcluster(const __half * W, const __half * X, int n, int N_out, int K, const WcOut & o, cudaStream_t s, bool pdl) {
     WB_CHECK(n >= 1 && n <= 256 && (N_out % 4) == 0, "gemm_wcluster handles 1..256 token rows, N_out %% 4 == 0 (got %d, %d)\n", n, N_out);
     const WcPlan p = wc_plan(n, N_out, K);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;
+    if (attr_set.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(gemm_wcluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
     }
     WB_CHECK(p.smem <= 200 * 1024, "gemm_wcluster: %d bytes of shared memory\n", p.smem);
     CUtensorMap tw, tx;
@@ -1087,10 +1086,9 @@ static int step_sm_count() {
 }
 
 static bool launch_cross(CrossArgs a, int n_rows, cudaStream_t s, bool pdl) {
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr;
+    if (attr.first()) {
         WB_CUDA_OK(cudaFuncSetAttribute(cross_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 132 * 1024));
-        attr = true;
     }
     a.items = a.H * n_rows;
     a.trace = trace_slot("cross");
@@ -1258,10 +1256,9 @@ struct LaneIssue {
     }
     // staging upload + token/position embedding + first LayerNorm
     bool begin() {
-        static bool attrs = false;
-        if (!attrs) {
+        static PerDeviceOnce attrs;
+        if (attrs.first()) {
             WB_CUDA_OK(cudaFuncSetAttribute(self_attn_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5120 * 4));
-            attrs = true;
         }
         WB_CHECK(S <= LN_THREADS * LN_MAX_PER_THREAD && (S % 64) == 0, "unsupported text state %d\n", S);
         WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage, ws.h_stage, SL.bytes, cudaMemcpyHostToDevice, s));
