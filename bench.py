@@ -52,6 +52,21 @@ def make_params(lib):
     return p
 
 
+class stdout_to_stderr:
+    """Context manager: file descriptor 1 is redirected to file descriptor 2 (catches C-level printf, not just sys.stdout)."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -177,8 +192,13 @@ def main():
         raise SystemExit("bench.py: no CUDA device — the b200 arm has no CPU path (use --impl reference for the CPU engine)")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries exactly one JSON line (rank 0)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # stdout carries exactly one JSON line (rank 0): NCCL prints its version banner with printf when NCCL_DEBUG is set, so file
+        # descriptor 1 points at stderr while the communicator comes up (eager init + the first collective)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        with stdout_to_stderr():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
 
     def barrier():
         if world > 1:

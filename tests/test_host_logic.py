@@ -143,3 +143,18 @@ def test_two_rank_gloo_gather_equals_single_process(ref_lib):
     assert m_a == m_b == merged1                                  # every rank holds the same, complete, ordered result
     assert [t0 for t0, _, _ in merged1] == sorted(t0 for t0, _, _ in merged1) or True
     assert merged1[-1][1] <= 6500 + 3000
+
+
+def test_bench_stdout_guard_moves_c_level_output_to_stderr(tmp_path):
+    """bench.py prints exactly one JSON line on stdout; library banners written to fd 1 while NCCL comes up must land on stderr"""
+    import subprocess
+    import sys as _sys
+    code = ("import os, sys; sys.path.insert(0, %r); import bench\n"
+            "print('before'); \n"
+            "with bench.stdout_to_stderr():\n"
+            "    os.write(1, b'banner from C\\n'); print('py inside')\n"
+            "print('after')\n") % str(ROOT)
+    r = subprocess.run([_sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.split() == ["before", "after"]
+    assert "banner from C" in r.stderr and "py inside" in r.stderr
