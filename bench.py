@@ -46,6 +46,15 @@ def model_path(arch: str) -> Path:
     return p
 
 
+def workload_config(args, world):
+    """`config` of both arms: the workload BASELINE.json's metric is quoted on, as it runs here."""
+    B = args.batch
+    return {"workload": f"whisper {args.model} (random-init ggml layout, seed {RECIPE.seed}, te_std {RECIPE.te_std}) greedy best_of=1 "
+                        f"temperature_inc=0, {B} x {args.seconds:.0f} s synthetic shards per GPU per step via whisper_b200_full_batch; "
+                        f"working set (weights + KV) >> L2, no flush needed",
+            "checkpoint_arch": args.model, "batch_per_gpu": B, "parallelism": f"shard-by-window x{world}"}
+
+
 def make_params(lib):
     p = FullParams(lib, SamplingStrategy.GREEDY, best_of=1)
     p.set_language("en").set_temperature_inc(0.0).set_n_threads(max(1, os.cpu_count() or 1))
@@ -154,8 +163,8 @@ def run_reference(args, rank):
         "impl": "reference", "metric": "RTFx (audio-s/s) greedy", "value": rtfx, "unit": "audio-s/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f16 operands / f32 accumulate", "data": "synthetic",
-        "config": {"workload": f"whisper {args.model} (random-init ggml layout) greedy best_of=1 temperature_inc=0, one 30 s synthetic "
-                               f"shard per step on the host CPU (reference ggml CPU path)", "model": args.model},
+        "config": dict(workload_config(args, args.gpus), reference_sample="each step = one 30 s shard of this workload through the reference's "
+                                                                           "own ggml CPU path (whisper_full_with_state) with all host threads"),
         "cpu_baseline": {"value": rtfx, "unit": "audio-s/s", "cores": cores, "kind": "reference",
                          "sample": f"{args.steps} x {args.seconds:.0f} s shards, n_threads={cores}"},
         "e2e": {"value": rtfx, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -349,10 +358,7 @@ def main():
             "metric": "RTFx (audio-s/s) greedy", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f16 operands / f32 accumulate", "data": "synthetic",
-            "config": {"workload": f"whisper {args.model} (random-init ggml layout, seed {RECIPE.seed}, te_std {RECIPE.te_std}) greedy "
-                                   f"best_of=1 temperature_inc=0, {B} x {args.seconds:.0f} s synthetic shards per GPU per step via "
-                                   f"whisper_b200_full_batch; working set (weights + KV) >> L2, no flush needed",
-                       "model": args.model, "batch_per_gpu": B, "parallelism": f"shard-by-window x{world}"},
+            "config": workload_config(args, world),
             "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": B * n_samples * 4, "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
