@@ -366,6 +366,11 @@ def main():
             "roofline": roofline,
             "roofline_next": roofline_next,
             "phase_ms_per_step_host_clock": phase,
+            # BASELINE.json's second quantity: encoder ms per 30 s window (whole encoder pass incl. cross K/V, host clock around
+            # the batched pass / windows), with the mel front end and the decode loop beside it
+            "encoder_ms_per_30s_window": round(phase["encode"] / B, 4),
+            "mel_ms_per_30s_window": round(phase["mel"] / B, 4),
+            "decode_ms_per_30s_window": round(max(0.0, ms_dev / args.steps - phase["encode"] - phase["mel"]) / B, 4),
             "kernel_breakdown_ms_per_step_est": {k: round(x / args.steps, 3) for k, x in sorted(est.items(), key=lambda kv: -kv[1])},
         }
         if world == 1 and not args.no_cpu_baseline and cf.ORACLE_LIB.exists():
