@@ -84,6 +84,14 @@ WHISPER_API int whisper_b200_test_cross_attn_step(const void * q_f16, const void
 WHISPER_API int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c, int iters, double * us_per_launch,
                                           double * bytes_per_launch);
 
+/* DTW token-timestamp kernels on HOST data (tests; replaces wc:8840-8890 + dtw_and_backtrace wc:8647-8731):
+ * qk f32 [n_heads][n_tok][T] softmax rows -> optional cost_out f32 [n_tok][n_audio]; path over rows sot_len .. n_tok-2.
+ * Returns the path length L (path_out[0..L) token indices, [L..2L) time indices) or < 0. */
+WHISPER_API int whisper_b200_test_dtw(const float * qk, int n_heads, int n_tok, int n_ctx, int n_audio, int medfilt_width, int sot_len,
+                                      float * cost_out, int32_t * path_out, int cap);
+/* dtw_and_backtrace alone on a host cost matrix cost[N][M] (time index contiguous) */
+WHISPER_API int whisper_b200_test_dtw_path(const float * cost, int N, int M, int32_t * path_out, int cap);
+
 #ifdef __cplusplus
 }
 #endif

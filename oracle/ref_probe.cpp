@@ -54,4 +54,64 @@ const float * ref_probe_aheads_qks(struct whisper_state * st, int64_t * n) {
     return st->aheads_cross_QKs_data.data();
 }
 
+
+// X1/X2 in isolation: the reference's own alignment post-processing (whisper.cpp:8840-8890: token-axis ggml_norm eps 1e-9, median
+// filter, mean over heads, negate, drop the sot sequence and eot) and dtw_and_backtrace (whisper.cpp:8647-8731) on a caller-supplied
+// alignment-head tensor in the layout of whisper_state::aheads_cross_QKs_data: data[head][audio_ctx][token].
+// cost_out (optional): [n_audio_tokens][N] floats, N = n_tokens - sot_len - 1 (token index contiguous, the ggml order of `w`).
+// Returns the path length L; path_out[0..L) = token indices, path_out[L..2L) = time indices (when cap >= 2L).
+int ref_probe_dtw(const float * data, int n_tokens, int n_audio_ctx, int n_heads, int n_audio_tokens, int sot_len, int medfilt_width,
+                  float * cost_out, int32_t * path_out, int cap) {
+    const size_t mem = (size_t) 64 * 1024 * 1024 + (size_t) n_tokens * n_audio_ctx * n_heads * 4 * 8;
+    struct ggml_init_params gparams = { mem, nullptr, false };
+    struct ggml_context * gctx = ggml_init(gparams);
+    ggml_tensor * w = ggml_new_tensor_3d(gctx, GGML_TYPE_F32, n_tokens, n_audio_tokens, n_heads);
+    for (int k = 0; k < n_heads; ++k)
+        for (int j = 0; j < n_audio_tokens; ++j)
+            memcpy((char *) w->data + j * w->nb[1] + k * w->nb[2], data + (size_t) j * n_tokens + (size_t) k * n_tokens * n_audio_ctx,
+                   n_tokens * sizeof(float));
+    w = ggml_norm(gctx, w, 1e-9f);
+    w = ggml_permute(gctx, ggml_permute(gctx, w, 2, 1, 0, 3), 0, 2, 1, 3);
+    median_filter_user_data mf_user_data = {medfilt_width};
+    w = ggml_map_custom1(gctx, w, median_filter, 1, &mf_user_data);
+    w = ggml_mean(gctx, w);
+    w = ggml_scale(gctx, w, -1.0);
+    w = ggml_reshape_2d(gctx, w, w->ne[1], w->ne[2]);
+    w = ggml_view_2d(gctx, w, w->ne[0] - sot_len - 1, w->ne[1], w->nb[1], sot_len * w->nb[0]);
+    struct ggml_cgraph * gf = ggml_new_graph(gctx);
+    ggml_build_forward_expand(gf, w);
+    ggml_backend_ptr backend { ggml_backend_init_by_type(GGML_BACKEND_DEVICE_TYPE_CPU, nullptr) };
+    ggml_backend_graph_compute(backend.get(), gf);
+    const int64_t N = w->ne[0], M = w->ne[1];
+    if (cost_out)
+        for (int64_t j = 0; j < M; ++j)
+            for (int64_t i = 0; i < N; ++i) cost_out[j * N + i] = whisper_get_f32_nd(w, i, j, 0, 0);
+    ggml_tensor * al = dtw_and_backtrace(gctx, w);
+    const int L = (int) al->ne[1];
+    if (path_out && cap >= 2 * L)
+        for (int i = 0; i < L; ++i) {
+            path_out[i] = whisper_get_i32_nd(al, 0, i, 0, 0);
+            path_out[L + i] = whisper_get_i32_nd(al, 1, i, 0, 0);
+        }
+    ggml_free(gctx);
+    return L;
+}
+
+// dtw_and_backtrace alone on a caller-supplied cost matrix cost[M][N] (token index contiguous)
+int ref_probe_dtw_path(const float * cost, int N, int M, int32_t * path_out, int cap) {
+    struct ggml_init_params gparams = { (size_t) 64 * 1024 * 1024 + (size_t) (N + 1) * (M + 1) * 16, nullptr, false };
+    struct ggml_context * gctx = ggml_init(gparams);
+    ggml_tensor * x = ggml_new_tensor_2d(gctx, GGML_TYPE_F32, N, M);
+    memcpy(x->data, cost, (size_t) N * M * sizeof(float));
+    ggml_tensor * al = dtw_and_backtrace(gctx, x);
+    const int L = (int) al->ne[1];
+    if (path_out && cap >= 2 * L)
+        for (int i = 0; i < L; ++i) {
+            path_out[i] = whisper_get_i32_nd(al, 0, i, 0, 0);
+            path_out[L + i] = whisper_get_i32_nd(al, 1, i, 0, 0);
+        }
+    ggml_free(gctx);
+    return L;
+}
+
 }

@@ -134,6 +134,11 @@ void whisper_free_context_params(struct whisper_context_params * params) { delet
 struct whisper_context * whisper_init_with_params_no_state(struct whisper_model_loader * loader, struct whisper_context_params params) {
     WB_TRY
     if (!loader || !loader->read) return nullptr;
+    if (!params.use_gpu) {
+        log_error("%s: use_gpu = false, but this library has no CPU path (sm_100a kernels only)\n", __func__);
+        if (loader->close) loader->close(loader->context);
+        return nullptr;
+    }
     if (params.flash_attn && params.dtw_token_timestamps) {
         // the reference drops DTW under flash attention (wc:3724-3727); this library's attention always exposes the
         // alignment-head softmax rows, so the request is honoured
@@ -252,8 +257,8 @@ int whisper_ctx_init_openvino_encoder(struct whisper_context *, const char *, co
 int whisper_pcm_to_mel_with_state(struct whisper_context * ctx, struct whisper_state * state, const float * samples, int n_samples, int) {
     WB_TRY
     if (!ctx || !state || !samples || n_samples < 0) return -1;
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!stage_pcm_to_mel(*state, samples, n_samples)) {
+    bool ok = false;
+    if (!sched_run(ctx, [&] { ok = stage_pcm_to_mel(*state, samples, n_samples); }) || !ok) {
         log_error("%s: failed to compute mel spectrogram\n", __func__);
         return -1;
     }
@@ -271,8 +276,8 @@ int whisper_set_mel_with_state(struct whisper_context * ctx, struct whisper_stat
         log_error("%s: invalid number of mel bands: %d (expected %d)\n", __func__, n_mel, ctx->model.filters_n_mel);
         return -1;
     }
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    return stage_set_mel(*state, data, n_len, n_mel) ? 0 : -1;
+    bool ok = false;
+    return sched_run(ctx, [&] { ok = stage_set_mel(*state, data, n_len, n_mel); }) && ok ? 0 : -1;
     WB_CATCH(-1)
 }
 int whisper_set_mel(struct whisper_context * ctx, const float * data, int n_len, int n_mel) {
@@ -282,9 +287,9 @@ int whisper_set_mel(struct whisper_context * ctx, const float * data, int n_len,
 int whisper_encode_with_state(struct whisper_context * ctx, struct whisper_state * state, int offset, int) {
     WB_TRY
     if (!ctx || !state) return -1;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     State * sp = state;
-    if (!stage_encode(*ctx, &sp, &offset, 1)) {
+    bool ok = false;
+    if (!sched_run(ctx, [&] { ok = stage_encode(*ctx, &sp, &offset, 1); }) || !ok) {
         log_error("%s: failed to eval\n", __func__);
         return -1;
     }
@@ -299,7 +304,6 @@ int whisper_decode_with_state(struct whisper_context * ctx, struct whisper_state
                               int) {
     WB_TRY
     if (!ctx || !state || !tokens || n_tokens <= 0) return 1;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     std::vector<BatchRow> rows;
     for (int i = 0; i < n_tokens; ++i) {
         if (tokens[i] < 0 || tokens[i] >= ctx->model.hp.n_vocab || n_past + i >= ctx->model.hp.n_text_ctx) {
@@ -308,8 +312,12 @@ int whisper_decode_with_state(struct whisper_context * ctx, struct whisper_state
         }
         rows.push_back(BatchRow{state, tokens[i], n_past + i, 0, i == n_tokens - 1});  // whisper_batch_prep_legacy wc:544-556
     }
-    state->kv_self.seq_rm(0, n_past, -1);
-    if (!stage_decode(*ctx, rows.data(), n_tokens, false) || !stage_fetch_logits(*ctx, rows.data(), n_tokens)) {
+    bool ok = false;
+    const bool ran = sched_run(ctx, [&] {
+        state->kv_self.seq_rm(0, n_past, -1);
+        ok = stage_decode(*ctx, rows.data(), n_tokens, false) && stage_fetch_logits(*ctx, rows.data(), n_tokens);
+    });
+    if (!ran || !ok) {
         log_error("%s: failed to eval\n", __func__);
         return 1;
     }
@@ -404,8 +412,9 @@ const char * whisper_lang_str_full(int id) {
 int whisper_lang_auto_detect_with_state(struct whisper_context * ctx, struct whisper_state * state, int offset_ms, int, float * lang_probs) {
     WB_TRY
     if (!ctx || !state) return -1;
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    return lang_auto_detect(ctx, state, offset_ms, lang_probs);
+    int r = -1;
+    if (!sched_run(ctx, [&] { r = lang_auto_detect(ctx, state, offset_ms, lang_probs); })) return -1;
+    return r;
     WB_CATCH(-1)
 }
 int whisper_lang_auto_detect(struct whisper_context * ctx, int offset_ms, int n_threads, float * lang_probs) {
@@ -503,12 +512,24 @@ void whisper_reset_timings(struct whisper_context * ctx) {
 // ---------------------------------------------------------------------------------------------
 // full transcription (wc:6795-7864) and result accessors (wc:7866-8033)
 // ---------------------------------------------------------------------------------------------
+// Options this library does not implement fail loudly instead of silently transcribing something else.
+static int unsupported_params(const whisper_full_params & params, const char * fn) {
+    if (params.grammar_rules != nullptr && params.n_grammar_rules > 0) {
+        log_error("%s: grammar-constrained sampling (grammar_rules) is not implemented by this library\n", fn);
+        return -10;
+    }
+    if (params.vad) {
+        log_error("%s: params.vad = true, but the Silero VAD front end is not implemented by this library\n", fn);
+        return -11;
+    }
+    return 0;
+}
+
 int whisper_full_with_state(struct whisper_context * ctx, struct whisper_state * state, struct whisper_full_params params, const float * samples,
                             int n_samples) {
     WB_TRY
     if (!ctx || !state) return -1;
-    if (params.vad) log_msg(GGML_LOG_LEVEL_WARN, "%s: the VAD front end is outside this library's path; processing all samples\n", __func__);
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (const int rc = unsupported_params(params, __func__)) return rc;
     State * sp = state;
     return full_with_states(ctx, &sp, 1, &params, false, &samples, &n_samples);
     WB_CATCH(-1)
@@ -529,7 +550,7 @@ int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state *
             if (states[j] == states[i]) return -1;
         sp[(size_t) i] = states[i];
     }
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (const int rc = unsupported_params(params, __func__)) return rc;
     return full_with_states(ctx, sp.data(), n_states, &params, false, samples, n_samples);
     WB_CATCH(-1)
 }
@@ -577,11 +598,7 @@ int whisper_full_parallel(struct whisper_context * ctx, struct whisper_full_para
         smp.push_back(samples + start);
         ns.push_back(n_cur);
     }
-    int ret;
-    {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        ret = full_with_states(ctx, sp.data(), (int) sp.size(), ps.data(), true, smp.data(), ns.data());
-    }
+    const int ret = full_with_states(ctx, sp.data(), (int) sp.size(), ps.data(), true, smp.data(), ns.data());
     const int64_t offset_t = (int64_t) (params.offset_ms / 10.0);
     State & main = *ctx->state;
     for (int i = 0; i < n_processors - 1; ++i) {
@@ -669,8 +686,8 @@ int whisper_b200_encode_batch(struct whisper_context * ctx, struct whisper_state
     WB_TRY
     if (!ctx || !states || !offsets || n_states <= 0) return -1;
     std::vector<State *> sp(states, states + n_states);
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    return stage_encode(*ctx, sp.data(), offsets, n_states) ? 0 : -1;
+    bool ok = false;
+    return sched_run(ctx, [&] { ok = stage_encode(*ctx, sp.data(), offsets, n_states); }) && ok ? 0 : -1;
     WB_CATCH(-1)
 }
 int whisper_b200_decode_batch(struct whisper_context * ctx, struct whisper_state ** states, const whisper_token * tokens, const int * n_past,
@@ -682,8 +699,8 @@ int whisper_b200_decode_batch(struct whisper_context * ctx, struct whisper_state
         rows.push_back(BatchRow{states[i], tokens[i], n_past[i], 0, true});
         states[i]->kv_self.seq_rm(0, n_past[i], -1);
     }
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!stage_decode(*ctx, rows.data(), n_states, false) || !stage_fetch_logits(*ctx, rows.data(), n_states)) return 1;
+    bool ok = false;
+    if (!sched_run(ctx, [&] { ok = stage_decode(*ctx, rows.data(), n_states, false) && stage_fetch_logits(*ctx, rows.data(), n_states); }) || !ok) return 1;
     return 0;
     WB_CATCH(1)
 }
@@ -968,6 +985,66 @@ int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c
     if (bytes_per_launch) *bytes_per_launch = r.bytes_per_launch;
     return 0;
     WB_CATCH(3)
+}
+
+
+// X1/X2 on caller-supplied HOST data (tests): qk [n_heads][n_tok][T] softmax rows -> cost [n_tok][n_audio] (host copy optional) and, over the
+// rows sot_len .. n_tok-2, the DTW path.  Returns the path length L (path_out[0..L) token indices, [L..2L) time indices), < 0 on failure.
+int whisper_b200_test_dtw(const float * qk, int n_heads, int n_tok, int T, int n_audio, int medfilt_width, int sot_len, float * cost_out,
+                          int32_t * path_out, int cap) {
+    WB_TRY
+    const int N = n_tok - sot_len - 1;
+    if (!qk || N <= 0 || n_audio <= medfilt_width || n_audio > T) return -1;
+    float *d_qk = nullptr, *d_nrm = nullptr, *d_cost = nullptr, *d_diag = nullptr;
+    int8_t * d_trace = nullptr;
+    int * d_path = nullptr;
+    const size_t capp = (size_t) N + n_audio;
+    std::vector<int> path(2 * capp + 1);
+    bool ok = cudaMalloc((void **) &d_qk, (size_t) n_heads * n_tok * T * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_nrm, (size_t) n_heads * n_tok * n_audio * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_cost, (size_t) n_tok * n_audio * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_diag, (size_t) 3 * (N + 1) * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_trace, (size_t) (N + 1) * (n_audio + 1)) == cudaSuccess &&
+              cudaMalloc((void **) &d_path, (2 * capp + 1) * 4) == cudaSuccess &&
+              cudaMemcpy(d_qk, qk, (size_t) n_heads * n_tok * T * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok) ok = dtw_cost(d_qk, n_heads, n_tok, T, n_audio, medfilt_width, d_nrm, d_cost, nullptr);
+    if (ok) ok = dtw_path(d_cost + (size_t) sot_len * n_audio, N, n_audio, d_diag, d_trace, d_path, d_path + 2 * capp, nullptr);
+    if (ok) ok = cudaMemcpy(path.data(), d_path, (2 * capp + 1) * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    if (ok && cost_out) ok = cudaMemcpy(cost_out, d_cost, (size_t) n_tok * n_audio * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    cudaFree(d_qk); cudaFree(d_nrm); cudaFree(d_cost); cudaFree(d_diag); cudaFree(d_trace); cudaFree(d_path);
+    if (!ok) return -2;
+    const int L = path[2 * capp];
+    if (path_out && cap >= 2 * L) {
+        memcpy(path_out, path.data() + (capp - (size_t) L), (size_t) L * 4);
+        memcpy(path_out + L, path.data() + capp + (capp - (size_t) L), (size_t) L * 4);
+    }
+    return L;
+    WB_CATCH(-3)
+}
+// dtw_and_backtrace alone (wc:8647-8731) on a HOST cost matrix cost[N][M] (time index contiguous)
+int whisper_b200_test_dtw_path(const float * cost, int N, int M, int32_t * path_out, int cap) {
+    WB_TRY
+    if (!cost || N <= 0 || M <= 0) return -1;
+    float *d_cost = nullptr, *d_diag = nullptr;
+    int8_t * d_trace = nullptr;
+    int * d_path = nullptr;
+    const size_t capp = (size_t) N + M;
+    std::vector<int> path(2 * capp + 1);
+    bool ok = cudaMalloc((void **) &d_cost, (size_t) N * M * 4) == cudaSuccess && cudaMalloc((void **) &d_diag, (size_t) 3 * (N + 1) * 4) == cudaSuccess &&
+              cudaMalloc((void **) &d_trace, (size_t) (N + 1) * (M + 1)) == cudaSuccess &&
+              cudaMalloc((void **) &d_path, (2 * capp + 1) * 4) == cudaSuccess &&
+              cudaMemcpy(d_cost, cost, (size_t) N * M * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok) ok = dtw_path(d_cost, N, M, d_diag, d_trace, d_path, d_path + 2 * capp, nullptr);
+    if (ok) ok = cudaMemcpy(path.data(), d_path, (2 * capp + 1) * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    cudaFree(d_cost); cudaFree(d_diag); cudaFree(d_trace); cudaFree(d_path);
+    if (!ok) return -2;
+    const int L = path[2 * capp];
+    if (path_out && cap >= 2 * L) {
+        memcpy(path_out, path.data() + (capp - (size_t) L), (size_t) L * 4);
+        memcpy(path_out + L, path.data() + capp + (capp - (size_t) L), (size_t) L * 4);
+    }
+    return L;
+    WB_CATCH(-3)
 }
 
 }  // extern "C"

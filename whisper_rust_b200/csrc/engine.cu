@@ -108,6 +108,7 @@ State::~State() {
 }
 
 Context::~Context() {
+    sched_shutdown(this);
     cudaSetDevice(model.device);
     if (stream) cudaStreamSynchronize(stream);
     step_release(*this);
@@ -118,7 +119,7 @@ Context::~Context() {
     if (dec_ws.h_out) cudaFreeHost(dec_ws.h_out);
     cudaFree(dec_ws.d_out);
     cudaFree(d_ahead_slot);
-    cudaFree(d_suppress);
+    masks.clear();
     if (stream) cudaStreamDestroy(stream);
 }
 
@@ -230,10 +231,6 @@ Context * context_create(whisper_model_loader * loader, whisper_context_params p
     }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         log_error("%s: failed to create stream\n", __func__);
-        delete ctx;
-        return nullptr;
-    }
-    if (cudaMalloc((void **) &ctx->d_suppress, 2 * (size_t) ctx->model.hp.n_vocab) != cudaSuccess) {
         delete ctx;
         return nullptr;
     }

@@ -5,6 +5,8 @@
 #pragma once
 
 #include <functional>
+#include <map>
+#include <memory>
 #include <mutex>
 #include <random>
 #include <set>
@@ -104,6 +106,15 @@ struct DecWorkspace {
 
 struct Context;
 
+// Static part of whisper_process_logits (wc:6195-6260) for one combination of (tdrz_enable, suppress_nst, suppress_regex): cached per
+// context, shared by every job with the same rules; jobs with different rules may share a sampler launch (SamplerRow::suppress).
+struct SuppressMask {
+    int device = 0;
+    uint8_t * d = nullptr;             // [2][V]: everything | the part that follows logits_filter_callback
+    std::vector<uint8_t> pre_host;     // the part the reference applies before logits_filter_callback (wc:6197-6224)
+    ~SuppressMask();
+};
+
 struct State {
     Context * ctx = nullptr;
 
@@ -155,7 +166,7 @@ struct Context {
     int64_t t_load_us = 0, t_start_us = 0;
 
     cudaStream_t stream = nullptr;
-    std::mutex mu;  // serialises device work issued through this context's shared workspaces
+    std::mutex mu;  // guards the lazy creation of the scheduler
     EncWorkspace enc_ws;
     DecWorkspace dec_ws;
     void * step = nullptr;  // decode-step graphs + their workspace (step.cu)
@@ -165,9 +176,9 @@ struct Context {
     std::vector<std::vector<int>> ahead_slot;  // [L][H]
     int * d_ahead_slot = nullptr;              // [L][H]
 
-    uint8_t * d_suppress = nullptr;            // [2][V] per-call suppress masks: everything | the part that follows logits_filter_callback
-    std::vector<uint8_t> suppress_host;        // everything
-    std::vector<uint8_t> suppress_pre_host;    // the part the reference applies before logits_filter_callback (wc:6197-6224)
+    std::map<std::string, std::shared_ptr<SuppressMask>> masks;  // only touched on the scheduler thread
+
+    void * sched = nullptr;  // the batching scheduler (full.cu): one worker thread per context owns all device work
 
     ~Context();
 };
@@ -205,11 +216,17 @@ bool stage_fetch_logits(Context & ctx, const BatchRow * rows, int n_rows);
 bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * srows, int n, bool copy_dists, Decoder ** decs,
                   const std::function<void(int, float *)> * prefilter = nullptr);
 
-bool build_suppress_mask(Context & ctx, const whisper_full_params & params);
+std::shared_ptr<SuppressMask> suppress_mask(Context & ctx, const whisper_full_params & params);
 
-// full transcription control loop (full.cpp)
+// ---- the batching scheduler (full.cu).  Every entry point that touches the device goes through the context's worker thread:
+// whisper_full_with_state / whisper_b200_full_batch / whisper_full_parallel submit jobs and block (user callbacks are handed back
+// to the calling thread); the worker advances all live jobs of the context in lock-step, admitting new ones at step boundaries.
+// Returns 0, or the first non-zero per-state code.  `params_per_state`: params[i] belongs to states[i], else params[0] to all.
 int full_with_states(Context * ctx, State * const * states, int n_states, const whisper_full_params * params, bool params_per_state,
                      const float * const * samples, const int * n_samples);
+// runs `fn` on the context's worker thread between device iterations (stage API: mel / encode / decode / probes); false if refused
+bool sched_run(Context * ctx, const std::function<void()> & fn);
+void sched_shutdown(Context * ctx);
 int lang_auto_detect(Context * ctx, State * st, int offset_ms, float * lang_probs);
 
 }  // namespace wb

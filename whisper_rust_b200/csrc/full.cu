@@ -11,6 +11,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
 #include <functional>
 #include <thread>
 #include <map>
@@ -31,11 +33,21 @@ static const char * const k_non_speech_tokens[] = {
     "))", "(((", ")))", "[[", "]]", "{{", "}}", "\xe2\x99\xaa\xe2\x99\xaa", "\xe2\x99\xaa\xe2\x99\xaa\xe2\x99\xaa", "\xe2\x99\xa9",
     "\xe2\x99\xaa", "\xe2\x99\xab", "\xe2\x99\xac", "\xe2\x99\xad", "\xe2\x99\xae", "\xe2\x99\xaf"};
 
-bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
+SuppressMask::~SuppressMask() {
+    if (d) {
+        cudaSetDevice(device);
+        cudaFree(d);
+    }
+}
+
+// Called on the scheduler thread only (the per-context cache is not locked).
+std::shared_ptr<SuppressMask> suppress_mask(Context & ctx, const whisper_full_params & params) {
+    const std::string key = std::string(params.tdrz_enable ? "1" : "0") + (params.suppress_nst ? "1" : "0") + (params.suppress_regex ? params.suppress_regex : "\x01");
+    auto hit = ctx.masks.find(key);
+    if (hit != ctx.masks.end()) return hit->second;
     const Vocab & vc = ctx.model.vocab;
     const int V = vc.n_vocab;
-    std::vector<uint8_t> & mk = ctx.suppress_host;
-    mk.assign((size_t) V, 0);
+    std::vector<uint8_t> mk((size_t) V, 0);
     auto kill = [&](int id) {
         if (id >= 0 && id < V) mk[(size_t) id] = 1;
     };
@@ -47,7 +59,9 @@ bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
     kill(vc.token_transcribe);
     kill(vc.token_prev);
     for (int i = 0; i < 100; ++i) kill(vc.token_sot + 1 + i);  // whisper_token_lang over the whole language table (wc:6219-6221)
-    ctx.suppress_pre_host = mk;  // everything above precedes logits_filter_callback in the reference (wc:6226-6228); what follows comes after it
+    auto m = std::make_shared<SuppressMask>();
+    m->device = ctx.model.device;
+    m->pre_host = mk;  // everything above precedes logits_filter_callback in the reference (wc:6226-6228); what follows comes after it
     if (params.suppress_regex != nullptr) {
         try {
             std::regex re(params.suppress_regex);
@@ -71,18 +85,22 @@ bool build_suppress_mask(Context & ctx, const whisper_full_params & params) {
         if (i2 != vc.token_to_id.end()) kill(i2->second);
     }
     std::vector<uint8_t> post((size_t) V);
-    for (int i = 0; i < V; ++i) post[(size_t) i] = mk[(size_t) i] && !ctx.suppress_pre_host[(size_t) i];
-    WB_CUDA_OK(cudaMemcpyAsync(ctx.d_suppress, mk.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream));
-    WB_CUDA_OK(cudaMemcpyAsync(ctx.d_suppress + V, post.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream));
-    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
-    return true;
+    for (int i = 0; i < V; ++i) post[(size_t) i] = mk[(size_t) i] && !m->pre_host[(size_t) i];
+    if (cudaMalloc((void **) &m->d, 2 * (size_t) V) != cudaSuccess) return nullptr;
+    if (cudaMemcpyAsync(m->d, mk.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream) != cudaSuccess ||
+        cudaMemcpyAsync(m->d + V, post.data(), (size_t) V, cudaMemcpyHostToDevice, ctx.stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx.stream) != cudaSuccess)
+        return nullptr;
+    if (ctx.masks.size() >= 64) ctx.masks.clear();  // a caller cycling through regexes: jobs keep their masks alive through the shared_ptr
+    ctx.masks[key] = m;
+    return m;
 }
 
 static SamplerStatic sampler_static(Context & ctx) {
     const Vocab & vc = ctx.model.vocab;
     SamplerStatic s{};
-    s.suppress = ctx.d_suppress;
-    s.suppress_post = ctx.d_suppress + vc.n_vocab;
+    s.suppress = nullptr;       // every sampler row carries its job's masks (SamplerRow::suppress)
+    s.suppress_post = nullptr;
     s.n_vocab = vc.n_vocab;
     s.token_eot = vc.token_eot;
     s.token_beg = vc.token_beg;
@@ -197,10 +215,20 @@ struct BeamCandidate {
     Sequence sequence;
 };
 
+struct Client;
+struct FullJob;
+// runs `fn` on the thread that submitted the job (blocked inside its whisper_full* call): user callbacks fire there (wh:461-480)
+static void call_owner(FullJob * job, const std::function<void()> & fn, bool is_logits_filter = false);
+
 struct FullJob {
     enum Phase { WINDOW_BEGIN, TEMP_BEGIN, AFTER_PROMPT, STEP, DONE };
 
     Context * ctx = nullptr;
+    Client * client = nullptr;                 // who waits for this job
+    std::shared_ptr<SuppressMask> mask;        // this job's static suppress rules
+    int lane = -1;                             // decode lane the job currently belongs to
+    bool admitted = false;
+    int64_t t_submit = 0;
     State * st = nullptr;
     whisper_full_params params{};
     const float * samples = nullptr;
@@ -242,6 +270,7 @@ struct FullJob {
 
     bool init();
     bool window_begin();   // true: this job needs its window encoded at `seek`
+    bool aborted();
     void after_encode();
     void temp_begin();
     void after_device();
@@ -377,14 +406,16 @@ bool FullJob::init() {
 bool FullJob::window_begin() {
     if (params.progress_callback) {
         const int progress_cur = (100 * (seek - seek_start)) / (seek_end - seek_start);
-        params.progress_callback(wctx(), wstate(), progress_cur, params.progress_callback_user_data);
+        call_owner(this, [&] { params.progress_callback(wctx(), wstate(), progress_cur, params.progress_callback_user_data); });
     }
     if (seek + delta_min >= seek_end) {
         finish(0);
         return false;
     }
     if (params.encoder_begin_callback) {
-        if (params.encoder_begin_callback(wctx(), wstate(), params.encoder_begin_callback_user_data) == false) {
+        bool go = true;
+        call_owner(this, [&] { go = params.encoder_begin_callback(wctx(), wstate(), params.encoder_begin_callback_user_data); });
+        if (go == false) {
             log_error("%s: encoder_begin_callback returned false - aborting\n", __func__);
             finish(0);
             return false;
@@ -393,8 +424,15 @@ bool FullJob::window_begin() {
     return true;
 }
 
+bool FullJob::aborted() {
+    if (!params.abort_callback) return false;
+    bool stop = false;
+    call_owner(this, [&] { stop = params.abort_callback(params.abort_callback_user_data); });
+    return stop;
+}
+
 void FullJob::after_encode() {
-    if (params.abort_callback && params.abort_callback(params.abort_callback_user_data)) {  // wc:2471
+    if (aborted()) {  // wc:2471
         log_error("%s: failed to encode\n", __func__);
         finish(-6);
         return;
@@ -426,6 +464,8 @@ SamplerRow FullJob::sampler_row(const Decoder & d, int logits_row, bool want_nos
     r.tid0 = d.seek_delta / 2;
     r.want_nosp = want_nosp ? 1 : 0;
     r.work_slot = logits_row;
+    r.suppress = mask->d;
+    r.suppress_post = mask->d + vc.n_vocab;
     return r;
 }
 
@@ -493,7 +533,7 @@ void FullJob::temp_begin() {
 
 // the device has run this job's rows: decoder forward + sampler
 void FullJob::after_device() {
-    if (params.abort_callback && params.abort_callback(params.abort_callback_user_data)) {  // wc:2993
+    if (aborted()) {  // wc:2993
         log_error("%s: failed to decode\n", __func__);
         finish(phase == AFTER_PROMPT ? -8 : -9);
         return;
@@ -813,7 +853,7 @@ void FullJob::emit_results() {
     };
     auto notify = [&](int n_new) {
         if (params.new_segment_callback && !ctx->params.dtw_token_timestamps)
-            params.new_segment_callback(wctx(), wstate(), n_new, params.new_segment_callback_user_data);
+            call_owner(this, [&] { params.new_segment_callback(wctx(), wstate(), n_new, params.new_segment_callback_user_data); });
     };
 
     if (!tokens_cur.empty() && ctx->model.n_loaded > 0 && !is_no_speech) {
@@ -861,7 +901,7 @@ void FullJob::emit_results() {
             dtw_token_timestamps(ctx, st, params, (int) result_all.size() - n_segments, (size_t) n_segments, seek, n_frames, 7);
             if (params.new_segment_callback) {
                 for (int seg = (int) result_all.size() - n_segments; seg < n_segments; seg++)
-                    params.new_segment_callback(wctx(), wstate(), seg, params.new_segment_callback_user_data);
+                    call_owner(this, [&] { params.new_segment_callback(wctx(), wstate(), seg, params.new_segment_callback_user_data); });
             }
         }
     }
@@ -1093,277 +1133,522 @@ int lang_auto_detect(Context * ctx, State * st, int offset_ms, float * lang_prob
 }
 
 // --------------------------------------------------------------------------------------------
-// the lock-step driver
+// the batching scheduler: continuous batching behind the unchanged whisper_full_with_state
 // --------------------------------------------------------------------------------------------
+// The reference lets many whisper_states of one context run concurrently from different threads (rs/whisper_state.rs:19-21,
+// wh:45-46), each call being its own CPU computation.  Here one worker thread per context owns the device: calls enqueue
+// their FullJob and block; the worker advances every live job of the context in lock-step (one batched decoder forward per
+// token), admits newly submitted jobs — and later windows of running ones — at step boundaries into the decode lanes, and
+// wakes each caller when its job is done.  whisper_b200_full_batch and whisper_full_parallel are clients of the same queue.
+// User callbacks are handed back to the thread that made the call and run there while the worker waits.
+struct Client {
+    std::condition_variable cv;
+    const std::function<void()> * pending_fn = nullptr;  // a callback the worker wants run on the owner's thread
+    bool fn_done = false;
+    int n_jobs = 0, n_done = 0;
+};
+
+struct Command {
+    const std::function<void()> * fn;
+    bool done = false;
+};
+
+struct Lane {
+    std::vector<FullJob *> jobs, enc_jobs, dev_jobs;
+    std::vector<State *> enc_states;
+    std::vector<int> enc_offsets;
+    std::vector<BatchRow> rows;
+    std::vector<SamplerRow> srows;
+    std::vector<Decoder *> sdecs;
+    std::vector<FullJob *> sjobs;  // the job behind every sampler row
+    bool pending = false;          // a fused step is in flight on this lane's stream
+    int n_lanes_at_launch = 1;
+};
+
+struct Scheduler {
+    Context * ctx;
+    std::mutex mu;
+    std::condition_variable cv_worker;
+    std::deque<FullJob *> submitted;    // jobs waiting for admission, in arrival order
+    std::deque<Command *> commands;     // stage-API closures to run on the worker
+    int64_t last_submit_us = 0;
+    bool stop = false;
+    bool in_logits_filter = false;      // the worker is inside a logits_filter_callback hand-off: shared workspaces are live
+    std::thread worker;
+    std::thread::id worker_id;
+
+    // worker-only state
+    std::vector<Lane> lanes;
+    int n_live = 0;
+    int max_lanes = 4, lane_rows = 256;
+
+    explicit Scheduler(Context * c) : ctx(c) {}
+    void main();
+    void run_commands(std::unique_lock<std::mutex> & lk);
+    template <typename Pred> void wait_serving(std::unique_lock<std::mutex> & lk, Pred pred);
+    void admit(std::vector<FullJob *> & incoming);
+    void encode_jobs(Lane & ln, const std::vector<FullJob *> & cand);
+    void lane_advance(int lane_id);
+    void lane_complete(int lane_id);
+    void reap();
+    void job_done(FullJob * j);
+    int active_lanes() const;
+};
+
+static Scheduler * scheduler_of(Context * ctx) {
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->sched) {
+        Scheduler * s = new Scheduler(ctx);
+        s->worker = std::thread([s] { s->main(); });
+        s->worker_id = s->worker.get_id();
+        ctx->sched = s;
+    }
+    return (Scheduler *) ctx->sched;
+}
+
+void sched_shutdown(Context * ctx) {
+    Scheduler * s;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        s = (Scheduler *) ctx->sched;
+        ctx->sched = nullptr;
+    }
+    if (!s) return;
+    {
+        std::lock_guard<std::mutex> lk(s->mu);
+        s->stop = true;
+    }
+    s->cv_worker.notify_all();
+    if (s->worker.joinable()) s->worker.join();
+    delete s;
+}
+
+// worker side: run queued stage-API closures (lock held on entry and exit)
+void Scheduler::run_commands(std::unique_lock<std::mutex> & lk) {
+    while (!commands.empty()) {
+        Command * c = commands.front();
+        commands.pop_front();
+        lk.unlock();
+        try {
+            (*c->fn)();
+        } catch (...) {
+            log_error("%s: exception in a stage call\n", __func__);
+        }
+        lk.lock();
+        c->done = true;
+        cv_worker.notify_all();  // command issuers wait on cv_worker too
+    }
+}
+
+// worker side: wait for pred() while staying responsive to stage-API closures (a user callback may call back into the library)
+template <typename Pred> void Scheduler::wait_serving(std::unique_lock<std::mutex> & lk, Pred pred) {
+    while (true) {
+        if (!in_logits_filter) run_commands(lk);
+        if (pred()) return;
+        cv_worker.wait(lk);
+    }
+}
+
+static void call_owner(FullJob * job, const std::function<void()> & fn, bool is_logits_filter) {
+    Scheduler * s = (Scheduler *) job->ctx->sched;
+    Client * c = job->client;
+    if (!s || !c || std::this_thread::get_id() != s->worker_id) {  // not under the scheduler (never the case today): run in place
+        fn();
+        return;
+    }
+    std::unique_lock<std::mutex> lk(s->mu);
+    c->pending_fn = &fn;
+    c->fn_done = false;
+    s->in_logits_filter = is_logits_filter;
+    c->cv.notify_all();
+    s->wait_serving(lk, [&] { return c->fn_done; });
+    s->in_logits_filter = false;
+}
+
+bool sched_run(Context * ctx, const std::function<void()> & fn) {
+    Scheduler * s = scheduler_of(ctx);
+    if (std::this_thread::get_id() == s->worker_id) {  // a stage call made from code already running on the worker
+        fn();
+        return true;
+    }
+    Command cmd{&fn};
+    std::unique_lock<std::mutex> lk(s->mu);
+    if (s->in_logits_filter) {
+        log_error("%s: stage calls on the same context from inside logits_filter_callback are not supported\n", __func__);
+        return false;
+    }
+    if (s->stop) return false;
+    s->commands.push_back(&cmd);
+    s->cv_worker.notify_all();
+    s->cv_worker.wait(lk, [&] { return cmd.done; });
+    return true;
+}
+
+void Scheduler::job_done(FullJob * j) {
+    std::lock_guard<std::mutex> lk(mu);
+    Client * c = j->client;
+    c->n_done++;
+    c->cv.notify_all();
+}
+
+// client side: submit the jobs, then serve callback hand-offs until every job has finished
 int full_with_states(Context * ctx, State * const * states, int n_states, const whisper_full_params * params_arr, bool params_per_state,
                      const float * const * samples, const int * n_samples) {
-    const int64_t t_call0 = time_us();
-    const whisper_full_params & params_in = params_arr[0];  // suppress rules / strategy are shared by the batch
-    if (cudaSetDevice(ctx->model.device) != cudaSuccess) return -6;
+    if (n_states <= 0) return 0;
+    Scheduler * s = scheduler_of(ctx);
+    if (std::this_thread::get_id() == s->worker_id) {
+        log_error("%s: whisper_full* called from inside a callback of the same context\n", __func__);
+        return -1;
+    }
+    Client client;
     std::vector<FullJob> jobs((size_t) n_states);
-    if (!build_suppress_mask(*ctx, params_in)) return -6;
-    const SamplerStatic sst = sampler_static(*ctx);
-
     for (int k = 0; k < n_states; ++k) {
         FullJob & j = jobs[(size_t) k];
         j.ctx = ctx;
         j.st = states[k];
-        j.params = params_per_state ? params_arr[k] : params_in;
+        j.client = &client;
+        j.params = params_per_state ? params_arr[k] : params_arr[0];
         j.samples = samples ? samples[k] : nullptr;
         j.n_samples = n_samples ? n_samples[k] : 0;
-        j.st->result_all.clear();
-        if (j.n_samples > 0) {  // wc:6806-6812
-            if (!stage_pcm_to_mel(*j.st, j.samples, j.n_samples)) {
-                log_error("%s: failed to compute log mel spectrogram\n", __func__);
-                j.finish(-2);
-                continue;
-            }
-        }
-        j.init();
+        j.t_submit = time_us();
     }
-
-    // ---- decode lanes (step.cuh): contiguous groups of jobs that advance independently.  A lane's fused decode step is
-    // launched without waiting; the host then serves the other lanes, so their kernels and this bookkeeping overlap.
-    struct Lane {
-        std::vector<FullJob *> jobs, enc_jobs, dev_jobs;
-        std::vector<State *> enc_states;
-        std::vector<int> enc_offsets;
-        std::vector<BatchRow> rows;
-        std::vector<SamplerRow> srows;
-        std::vector<Decoder *> sdecs;
-        std::vector<FullJob *> sjobs;  // the job behind every sampler row
-        bool pending = false;
-    };
-    int n_lanes = 1;
-    {
-        const char * e = getenv("WB200_LANES");
-        if (e && atoi(e) > 0) n_lanes = atoi(e);
-        else n_lanes = std::max(std::min(4, n_states / 64), (n_states + 255) / 256);  // measured on B200: 4 lanes of 64-96 rows
-                                                                                      // beat one of 256 by ~5 %; a lane's fused step takes at most 256 rows
-        n_lanes = std::max(1, std::min(n_lanes, std::min(n_states, step_max_lanes())));
+    client.n_jobs = n_states;
+    std::unique_lock<std::mutex> lk(s->mu);
+    if (s->stop) return -1;
+    for (auto & j : jobs) s->submitted.push_back(&j);
+    s->last_submit_us = time_us();
+    s->cv_worker.notify_all();
+    while (client.n_done < client.n_jobs) {
+        if (client.pending_fn) {
+            const std::function<void()> * fn = client.pending_fn;
+            client.pending_fn = nullptr;
+            lk.unlock();
+            try {
+                (*fn)();
+            } catch (...) {
+                log_error("%s: a user callback threw\n", __func__);
+            }
+            lk.lock();
+            client.fn_done = true;
+            s->cv_worker.notify_all();
+            continue;
+        }
+        client.cv.wait(lk);
     }
-    std::vector<Lane> lanes((size_t) n_lanes);
-    for (int k = 0; k < n_states; ++k) lanes[(size_t) ((int64_t) k * n_lanes / n_states)].jobs.push_back(&jobs[(size_t) k]);
-
-    auto encode_jobs = [&](Lane & ln, const std::vector<Lane *> & from) {
-        ln.enc_states.clear();
-        ln.enc_offsets.clear();
-        ln.enc_jobs.clear();
-        for (Lane * src : from)
-            for (FullJob * j : src->jobs) {
-                if (j->phase != FullJob::WINDOW_BEGIN) continue;
-                if (j->window_begin()) {
-                    ln.enc_states.push_back(j->st);
-                    ln.enc_offsets.push_back(j->seek);
-                    ln.enc_jobs.push_back(j);
-                }
-            }
-        if (ln.enc_jobs.empty()) return;
-        if (getenv("WB200_HOST_PROF")) fprintf(stderr, "host_prof: t=%.1f ms encode %zu windows\n", (time_us() - t_call0) / 1e3, ln.enc_jobs.size());
-        if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
-            log_error("%s: failed to encode\n", __func__);
-            for (auto * j : ln.enc_jobs) j->finish(-6);
-        } else {
-            for (auto * j : ln.enc_jobs) j->after_encode();
-        }
-    };
-    // the first windows of every lane go through the encoder as one batch
-    {
-        std::vector<Lane *> all;
-        for (auto & ln : lanes) all.push_back(&ln);
-        encode_jobs(lanes[0], all);
-    }
-
-    // WB200_HOST_PROF=1: where the host time of the token loop goes (printed once per call)
-    const bool host_prof = getenv("WB200_HOST_PROF") != nullptr;
-    int64_t hp_gather = 0, hp_elig = 0, hp_launch = 0, hp_wait = 0, hp_after = 0, hp_steps = 0;
-    std::string hp_log;
-    int hp_last_n[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
-    // Jobs that come back for a later window of their audio (seek advanced by less than the window) have fallen out of step
-    // with their lane; instead of each decoding alone on its own lane they are handed to lane 0, which runs them as one batch.
-    std::vector<FullJob *> adopt;
-    // advances a lane until it has a fused step in flight (pending) or nothing left to do
-    auto lane_advance = [&](Lane & ln, int lane_id) {
-        while (true) {
-            const int64_t tg0 = host_prof ? time_us() : 0;
-            if (n_lanes > 1) {
-                if (lane_id == 0) {
-                    ln.jobs.insert(ln.jobs.end(), adopt.begin(), adopt.end());
-                    adopt.clear();
-                } else {
-                    for (size_t q = 0; q < ln.jobs.size();) {
-                        FullJob * j = ln.jobs[q];
-                        if (j->phase == FullJob::WINDOW_BEGIN && j->seek > j->seek_start && j->seek + FullJob::delta_min < j->seek_end) {
-                            adopt.push_back(j);
-                            ln.jobs.erase(ln.jobs.begin() + (long) q);
-                        } else {
-                            ++q;
-                        }
-                    }
-                }
-            }
-            // ---- windows that need their encoder pass
-            encode_jobs(ln, {&ln});
-            // ---- gather the decoder rows of every live job
-            ln.rows.clear();
-            ln.srows.clear();
-            ln.sdecs.clear();
-            ln.sjobs.clear();
-            ln.dev_jobs.clear();
-            bool any_live = false, any_dists = false;
-            // Jobs that contribute several rows (prompt passes, beams) take the general decoder path, jobs with one row per
-            // state the fused step.  When both kinds are waiting, the multi-row jobs go first on their own: which path a
-            // token is computed on then depends on the job alone, never on what else happens to share the iteration.
-            bool has_multi = false, has_single = false;
-            for (FullJob * jp : ln.jobs) {
-                FullJob & j = *jp;
-                if (j.phase == FullJob::DONE) continue;
-                if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
-                if ((j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) || j.rows.empty()) continue;
-                if (j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback) has_single = true;
-                else has_multi = true;
-            }
-            for (FullJob * jp : ln.jobs) {
-                FullJob & j = *jp;
-                if (j.phase == FullJob::DONE) continue;
-                any_live = true;
-                if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
-                if (j.rows.empty()) continue;
-                if (has_multi && has_single && j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback)
-                    continue;  // waits for the next iteration
-                // flagged rows of this job map to consecutive logits rows
-                int flagged = 0;
-                for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
-                const int base = (int) ln.srows.size();
-                if (flagged != (int) j.srows.size()) {
-                    log_error("%s: internal error: %d flagged rows vs %zu sampler rows\n", __func__, flagged, j.srows.size());
-                    j.finish(-9);
-                    continue;
-                }
-                ln.rows.insert(ln.rows.end(), j.rows.begin(), j.rows.end());
-                for (size_t q = 0; q < j.srows.size(); ++q) {
-                    SamplerRow sr = j.srows[q];
-                    sr.logits_row = base + (int) q;
-                    sr.work_slot = base + (int) q;
-                    sr.prefiltered = j.params.logits_filter_callback ? 1 : 0;
-                    ln.srows.push_back(sr);
-                    ln.sdecs.push_back(j.sdecs[q]);
-                    ln.sjobs.push_back(&j);
-                    any_dists = any_dists || j.sdecs[q]->want_dists;
-                }
-                ln.dev_jobs.push_back(&j);
-            }
-            if (!any_live) return;
-            if (ln.dev_jobs.empty()) continue;
-
-            // logits_filter_callback (wh:474-480, wc:6226-6228) mutates HOST logits between the static suppressions and the
-            // timestamp rules: those rows take the general path, the host applies everything the reference applies before the
-            // callback, calls it, and the device sampler continues from there (SamplerRow::prefiltered)
-            bool any_callback = false;
-            for (const SamplerRow & sr : ln.srows) any_callback = any_callback || sr.prefiltered;
-            const std::function<void(int, float *)> prefilter = [&](int q, float * lg) {
-                FullJob & j = *ln.sjobs[(size_t) q];
-                const Decoder & d = *ln.sdecs[(size_t) q];
-                const SamplerRow & r = ln.srows[(size_t) q];
-                const Vocab & vc = ctx->model.vocab;
-                const int V = vc.n_vocab;
-                if (r.temperature > 0.0f)
-                    for (int k = 0; k < V; ++k) lg[k] /= r.temperature;
-                if (r.suppress_blank && r.is_initial) {
-                    lg[vc.token_eot] = -INFINITY;
-                    if (sst.token_space >= 0) lg[sst.token_space] = -INFINITY;
-                }
-                for (int k = 0; k < V; ++k)
-                    if (ctx->suppress_pre_host[(size_t) k]) lg[k] = -INFINITY;
-                if (r.no_timestamps)
-                    for (int k = vc.token_beg; k < V; ++k) lg[k] = -INFINITY;
-                j.params.logits_filter_callback(j.wctx(), j.wstate(), d.sequence.tokens.data(), (int) d.sequence.tokens.size(), lg,
-                                                j.params.logits_filter_callback_user_data);
-            };
-            const int n_rows = (int) ln.rows.size();
-            const int64_t tg1 = host_prof ? time_us() : 0;
-            const bool fused_step = !any_callback && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
-            const int64_t tg2 = host_prof ? time_us() : 0;
-            hp_gather += tg1 - tg0;
-            hp_elig += tg2 - tg1;
-            bool ok;
-            if (fused_step) {
-                // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
-                ok = stage_step_launch(*ctx, lane_id, n_lanes, ln.rows.data(), n_rows, sst, ln.srows.data());
-                if (host_prof) {
-                    hp_launch += time_us() - tg2, ++hp_steps;
-                    if (n_rows != hp_last_n[lane_id & 7]) {  // log changes of a lane's row count with their time
-                        hp_log += " [t=" + std::to_string((time_us() - t_call0) / 1000) + "ms lane" + std::to_string(lane_id) + " n=" + std::to_string(n_rows) + "]";
-                        hp_last_n[lane_id & 7] = n_rows;
-                    }
-                }
-                if (ok) {
-                    ln.pending = true;
-                    return;
-                }
-            } else {
-                ok = stage_decode(*ctx, ln.rows.data(), n_rows, false) &&
-                     stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data(), any_callback ? &prefilter : nullptr);
-            }
-            if (!ok) {
-                log_error("%s: failed to decode\n", __func__);
-                for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
-                continue;
-            }
-            for (auto * j : ln.dev_jobs) j->after_device();
-        }
-    };
-    auto lane_complete = [&](Lane & ln, int lane_id) {
-        ln.pending = false;
-        const int64_t tw0 = host_prof ? time_us() : 0;
-        if (!stage_step_wait(*ctx, lane_id, ln.rows.data(), (int) ln.rows.size(), ln.sdecs.data())) {
-            log_error("%s: failed to decode\n", __func__);
-            for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
-            return;
-        }
-        const int64_t tw1 = host_prof ? time_us() : 0;
-        for (auto * j : ln.dev_jobs) j->after_device();
-        if (host_prof) hp_wait += tw1 - tw0, hp_after += time_us() - tw1;
-    };
-
-    if (n_lanes > 1) cudaStreamSynchronize(ctx->stream);  // lanes > 0 run on their own streams: everything queued so far is done
-    for (int l = 0; l < n_lanes; ++l) lane_advance(lanes[(size_t) l], l);
-    int trace_round = getenv("WB200_STEP_TRACE") ? 0 : -1;
-    while (true) {
-        if (trace_round >= 0 && ++trace_round == 100) {
-            // in-situ timeline (step.cuh): drain every lane, dump the stamps of their last (concurrent) steps, resume
-            for (int l = 0; l < n_lanes; ++l)
-                if (lanes[(size_t) l].pending) lane_complete(lanes[(size_t) l], l);
-            step_trace_dump(*ctx);
-            for (int l = 0; l < n_lanes; ++l) lane_advance(lanes[(size_t) l], l);
-        }
-        // serve whichever lane finishes first (a fixed round-robin would hold every lane to the slowest one's pace)
-        bool any_pending = false, served = false;
-        for (int l = 0; l < n_lanes; ++l) {
-            Lane & ln = lanes[(size_t) l];
-            if (!ln.pending) continue;
-            any_pending = true;
-            if (n_lanes > 1 && !stage_step_ready(*ctx, l)) continue;
-            served = true;
-            lane_complete(ln, l);
-            lane_advance(ln, l);
-        }
-        if (!adopt.empty() && !lanes[0].pending) lane_advance(lanes[0], 0);
-        any_pending = false;
-        for (int l = 0; l < n_lanes; ++l) any_pending = any_pending || lanes[(size_t) l].pending;
-        if (!any_pending) break;
-        if (!served) std::this_thread::yield();
-    }
-    if (host_prof) fprintf(stderr, "host_prof: total %.1f ms; row-count changes:%s\n", (time_us() - t_call0) / 1e3, hp_log.c_str());
-    if (host_prof)
-        fprintf(stderr, "host_prof: %lld fused steps; us/step: gather %.1f eligible %.1f launch %.1f wait %.1f after_device %.1f\n", (long long) hp_steps,
-                hp_gather / (double) std::max<int64_t>(1, hp_steps), hp_elig / (double) std::max<int64_t>(1, hp_steps),
-                hp_launch / (double) std::max<int64_t>(1, hp_steps), hp_wait / (double) std::max<int64_t>(1, hp_steps),
-                hp_after / (double) std::max<int64_t>(1, hp_steps));
+    lk.unlock();
     int ret = 0;
     for (auto & j : jobs)
         if (j.ret != 0 && ret == 0) ret = j.ret;
     return ret;
+}
+
+// ---- worker side ------------------------------------------------------------------------------------------------------
+int Scheduler::active_lanes() const {
+    int n = 0;
+    for (const Lane & ln : lanes) n += ln.jobs.empty() ? 0 : 1;
+    return std::max(1, n);
+}
+
+// window heads (callbacks, end-of-audio test) and ONE batched encoder pass for every candidate that starts a window
+void Scheduler::encode_jobs(Lane & ln, const std::vector<FullJob *> & cand) {
+    ln.enc_states.clear();
+    ln.enc_offsets.clear();
+    ln.enc_jobs.clear();
+    for (FullJob * j : cand) {
+        if (j->phase != FullJob::WINDOW_BEGIN) continue;
+        if (j->window_begin()) {
+            ln.enc_states.push_back(j->st);
+            ln.enc_offsets.push_back(j->seek);
+            ln.enc_jobs.push_back(j);
+        }
+    }
+    if (ln.enc_jobs.empty()) return;
+    if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
+        log_error("%s: failed to encode\n", __func__);
+        for (auto * j : ln.enc_jobs) j->finish(-6);
+    } else {
+        for (auto * j : ln.enc_jobs) j->after_encode();
+    }
+    ln.enc_jobs.clear();
+}
+
+// mel, call set-up (wc:6801-6984), lane assignment and the first encoder pass of newly submitted jobs
+void Scheduler::admit(std::vector<FullJob *> & incoming) {
+    std::vector<FullJob *> fresh;
+    for (FullJob * j : incoming) {
+        j->admitted = true;
+        j->st->result_all.clear();
+        j->mask = suppress_mask(*ctx, j->params);
+        if (!j->mask) {
+            j->finish(-6);
+        } else if (j->n_samples > 0 && !stage_pcm_to_mel(*j->st, j->samples, j->n_samples)) {  // wc:6806-6812
+            log_error("%s: failed to compute log mel spectrogram\n", "whisper_full_with_state");
+            j->finish(-2);
+        } else {
+            j->init();
+        }
+        if (j->phase == FullJob::DONE) job_done(j);
+        else fresh.push_back(j);
+    }
+    if (fresh.empty()) return;
+    // lanes (step.cuh): groups of jobs that advance independently.  Measured on B200: 4 lanes of 64-96 rows beat one
+    // of 256 by ~5 %; below 128 sequences one lane streams the decoder weights once for all of them
+    const int total = n_live + (int) fresh.size();
+    int target;
+    const char * e = getenv("WB200_LANES");
+    if (e && atoi(e) > 0) target = std::min(atoi(e), total);
+    else target = std::max(std::min(max_lanes, total / 64), (total + lane_rows - 1) / lane_rows);
+    target = std::max(1, std::min(target, (int) lanes.size()));
+    for (size_t k = 0; k < fresh.size(); ++k) {
+        int best = 0;
+        for (int l = 1; l < target; ++l)
+            if (lanes[(size_t) l].jobs.size() < lanes[(size_t) best].jobs.size()) best = l;
+        fresh[k]->lane = best;
+        lanes[(size_t) best].jobs.push_back(fresh[k]);
+    }
+    n_live += (int) fresh.size();
+    Lane scratch;
+    encode_jobs(scratch, fresh);  // the first windows of every lane go through the encoder as one batch
+}
+
+void Scheduler::reap() {
+    for (Lane & ln : lanes) {
+        bool any = false;
+        for (FullJob * j : ln.jobs) any = any || j->phase == FullJob::DONE;
+        if (!any) continue;
+        std::vector<FullJob *> keep, done;
+        for (FullJob * j : ln.jobs) (j->phase == FullJob::DONE ? done : keep).push_back(j);
+        ln.jobs.swap(keep);
+        if (!ln.pending) {
+            ln.dev_jobs.clear();
+            ln.sjobs.clear();
+            ln.sdecs.clear();
+        }
+        n_live -= (int) done.size();
+        for (FullJob * j : done) job_done(j);  // the job's memory belongs to its caller from here on
+    }
+}
+
+// advances a lane until it has a fused step in flight (pending) or nothing left to do
+void Scheduler::lane_advance(int lane_id) {
+    Lane & ln = lanes[(size_t) lane_id];
+    const SamplerStatic sst = sampler_static(*ctx);
+    while (true) {
+        // Jobs that come back for a later window of their audio have fallen out of step with their lane; with several lanes
+        // active they are handed to lane 0, which runs them as one batch instead of each decoding alone on its own lane.
+        if (lane_id != 0 && active_lanes() > 1) {
+            for (size_t q = 0; q < ln.jobs.size();) {
+                FullJob * j = ln.jobs[q];
+                if (j->phase == FullJob::WINDOW_BEGIN && j->seek > j->seek_start && j->seek + FullJob::delta_min < j->seek_end &&
+                    (int) lanes[0].jobs.size() < lane_rows) {
+                    j->lane = 0;
+                    lanes[0].jobs.push_back(j);
+                    ln.jobs.erase(ln.jobs.begin() + (long) q);
+                } else {
+                    ++q;
+                }
+            }
+        }
+        // ---- windows that need their encoder pass
+        encode_jobs(ln, ln.jobs);
+        // ---- gather the decoder rows of every live job
+        ln.rows.clear();
+        ln.srows.clear();
+        ln.sdecs.clear();
+        ln.sjobs.clear();
+        ln.dev_jobs.clear();
+        bool any_live = false, any_dists = false;
+        // Jobs that contribute several rows (prompt passes, beams) take the general decoder path, jobs with one row per
+        // state the fused step.  When both kinds are waiting, the multi-row jobs go first on their own: which path a
+        // token is computed on then depends on the job alone, never on what else happens to share the iteration.
+        bool has_multi = false, has_single = false;
+        for (FullJob * jp : ln.jobs) {
+            FullJob & j = *jp;
+            if (j.phase == FullJob::DONE) continue;
+            if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
+            if ((j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) || j.rows.empty()) continue;
+            if (j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback) has_single = true;
+            else has_multi = true;
+        }
+        for (FullJob * jp : ln.jobs) {
+            FullJob & j = *jp;
+            if (j.phase == FullJob::DONE) continue;
+            any_live = true;
+            if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
+            if (j.rows.empty()) continue;
+            const bool single = j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback;
+            if (has_multi && has_single && single) continue;  // waits for the next iteration
+            if (single && (int) ln.rows.size() >= lane_rows) continue;
+            // flagged rows of this job map to consecutive logits rows
+            int flagged = 0;
+            for (const auto & r : j.rows) flagged += r.want_logits ? 1 : 0;
+            const int base = (int) ln.srows.size();
+            if (flagged != (int) j.srows.size()) {
+                log_error("%s: internal error: %d flagged rows vs %zu sampler rows\n", __func__, flagged, j.srows.size());
+                j.finish(-9);
+                continue;
+            }
+            ln.rows.insert(ln.rows.end(), j.rows.begin(), j.rows.end());
+            for (size_t q = 0; q < j.srows.size(); ++q) {
+                SamplerRow sr = j.srows[q];
+                sr.logits_row = base + (int) q;
+                sr.work_slot = base + (int) q;
+                sr.prefiltered = j.params.logits_filter_callback ? 1 : 0;
+                ln.srows.push_back(sr);
+                ln.sdecs.push_back(j.sdecs[q]);
+                ln.sjobs.push_back(&j);
+                any_dists = any_dists || j.sdecs[q]->want_dists;
+            }
+            ln.dev_jobs.push_back(&j);
+        }
+        if (!any_live) return;
+        if (ln.dev_jobs.empty()) {
+            bool progress = false;  // a job may have just finished or moved to another window: look again, else stop
+            for (FullJob * jp : ln.jobs) progress = progress || jp->phase == FullJob::WINDOW_BEGIN || jp->phase == FullJob::TEMP_BEGIN;
+            if (!progress) return;
+            continue;
+        }
+
+        // logits_filter_callback (wh:474-480, wc:6226-6228) mutates HOST logits between the static suppressions and the
+        // timestamp rules: those rows take the general path, the host applies everything the reference applies before the
+        // callback, calls it on the caller's thread, and the device sampler continues from there (SamplerRow::prefiltered)
+        bool any_callback = false;
+        for (const SamplerRow & sr : ln.srows) any_callback = any_callback || sr.prefiltered;
+        const std::function<void(int, float *)> prefilter = [&](int q, float * lg) {
+            FullJob & j = *ln.sjobs[(size_t) q];
+            const Decoder & d = *ln.sdecs[(size_t) q];
+            const SamplerRow & r = ln.srows[(size_t) q];
+            const Vocab & vc = ctx->model.vocab;
+            const int V = vc.n_vocab;
+            if (r.temperature > 0.0f)
+                for (int k = 0; k < V; ++k) lg[k] /= r.temperature;
+            if (r.suppress_blank && r.is_initial) {
+                lg[vc.token_eot] = -INFINITY;
+                if (sst.token_space >= 0) lg[sst.token_space] = -INFINITY;
+            }
+            for (int k = 0; k < V; ++k)
+                if (j.mask->pre_host[(size_t) k]) lg[k] = -INFINITY;
+            if (r.no_timestamps)
+                for (int k = vc.token_beg; k < V; ++k) lg[k] = -INFINITY;
+            call_owner(&j, [&] {
+                j.params.logits_filter_callback(j.wctx(), j.wstate(), d.sequence.tokens.data(), (int) d.sequence.tokens.size(), lg,
+                                                j.params.logits_filter_callback_user_data);
+            }, true);
+        };
+        const int n_rows = (int) ln.rows.size();
+        const bool fused_step = !any_callback && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
+        bool ok;
+        if (fused_step) {
+            // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
+            ok = stage_step_launch(*ctx, lane_id, active_lanes(), ln.rows.data(), n_rows, sst, ln.srows.data());
+            if (ok) {
+                ln.pending = true;
+                return;
+            }
+        } else {
+            ok = stage_decode(*ctx, ln.rows.data(), n_rows, false) &&
+                 stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data(), any_callback ? &prefilter : nullptr);
+        }
+        if (!ok) {
+            log_error("%s: failed to decode\n", __func__);
+            for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
+            continue;
+        }
+        for (auto * j : ln.dev_jobs) j->after_device();
+    }
+}
+
+void Scheduler::lane_complete(int lane_id) {
+    Lane & ln = lanes[(size_t) lane_id];
+    ln.pending = false;
+    if (!stage_step_wait(*ctx, lane_id, ln.rows.data(), (int) ln.rows.size(), ln.sdecs.data())) {
+        log_error("%s: failed to decode\n", __func__);
+        for (auto * j : ln.dev_jobs) j->finish(j->phase == FullJob::AFTER_PROMPT ? -8 : -9);
+        return;
+    }
+    for (auto * j : ln.dev_jobs) j->after_device();
+}
+
+void Scheduler::main() {
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        worker_id = std::this_thread::get_id();
+    }
+    cudaSetDevice(ctx->model.device);
+    lanes.assign((size_t) step_max_lanes(), Lane());
+    int trace_steps = getenv("WB200_STEP_TRACE") ? 0 : -1;
+    std::unique_lock<std::mutex> lk(mu);
+    while (true) {
+        wait_serving(lk, [&] { return stop || !submitted.empty() || n_live > 0; });
+        if (stop && n_live == 0) {
+            // jobs still queued at shutdown are failed, their callers released
+            while (!submitted.empty()) {
+                FullJob * j = submitted.front();
+                submitted.pop_front();
+                j->ret = -1;
+                j->client->n_done++;
+                j->client->cv.notify_all();
+            }
+            break;
+        }
+        // ---- admission: wait until arrivals have paused (callers arriving in a burst become ONE encoder batch and one decode
+        // cohort), bounded by how long the oldest caller has waited; longer pauses are accepted while other jobs keep the device busy
+        std::vector<FullJob *> incoming;
+        if (!submitted.empty()) {
+            const int64_t now = time_us();
+            const bool idle = n_live == 0;
+            const int64_t settle = idle ? 150 : 1000, max_wait = idle ? 2000 : 20000;
+            const bool go = now - last_submit_us >= settle || now - submitted.front()->t_submit >= max_wait || stop;
+            if (go) {
+                const int room = (int) lanes.size() * lane_rows - n_live;
+                while (!submitted.empty() && (int) incoming.size() < room) {
+                    incoming.push_back(submitted.front());
+                    submitted.pop_front();
+                }
+            } else if (idle) {
+                cv_worker.wait_for(lk, std::chrono::microseconds(settle));
+                continue;
+            }
+        }
+        lk.unlock();
+        try {
+            if (!incoming.empty()) admit(incoming);
+            int n_pending = 0;
+            for (size_t l = 0; l < lanes.size(); ++l) {
+                if (!lanes[l].pending && !lanes[l].jobs.empty()) lane_advance((int) l);
+                n_pending += lanes[l].pending ? 1 : 0;
+            }
+            bool served = false;
+            for (size_t l = 0; l < lanes.size(); ++l) {
+                Lane & ln = lanes[l];
+                if (!ln.pending) continue;
+                // serve whichever lane finishes first (a fixed round-robin would hold every lane to the slowest one's pace); a lane
+                // that is alone is simply waited for
+                if (n_pending > 1 && !stage_step_ready(*ctx, (int) l)) continue;
+                served = true;
+                lane_complete((int) l);
+                lane_advance((int) l);
+                if (trace_steps >= 0 && ++trace_steps == 100) {
+                    // in-situ timeline (step.cuh): drain every lane, dump the stamps of their last (concurrent) steps, resume
+                    for (size_t q = 0; q < lanes.size(); ++q)
+                        if (lanes[q].pending) lane_complete((int) q);
+                    step_trace_dump(*ctx);
+                }
+            }
+            reap();
+            if (!served && n_pending > 0) std::this_thread::yield();
+        } catch (const std::exception & ex) {
+            log_error("%s: exception on the scheduler thread: %s\n", __func__, ex.what());
+            for (Lane & ln : lanes) {
+                if (ln.pending) cudaStreamSynchronize(nullptr);
+                ln.pending = false;
+                for (FullJob * j : ln.jobs)
+                    if (j->phase != FullJob::DONE) j->finish(-1);
+            }
+            reap();
+        }
+        lk.lock();
+    }
 }
 
 }  // namespace wb

@@ -708,6 +708,8 @@ sampler_kernel(SamplerStatic st, const float * __restrict__ logits_all, int64_t 
     float * lg = work + (int64_t) r.work_slot * 3 * V;  // filtered logits
     float * lp = lg + V;                                // logprobs
     float * pr = lp + V;                                // probs
+    const uint8_t * __restrict__ sup      = r.suppress ? r.suppress : st.suppress;
+    const uint8_t * __restrict__ sup_post = r.suppress_post ? r.suppress_post : st.suppress_post;
 
     // no-speech probability from the raw logits (whisper.cpp:7126-7134)
     float nosp = 0.0f;
@@ -730,11 +732,11 @@ sampler_kernel(SamplerStatic st, const float * __restrict__ logits_all, int64_t 
         bool kill;
         if (r.prefiltered) {
             x = lg[i];
-            kill = st.suppress_post[i] != 0;
+            kill = sup_post[i] != 0;
         } else {
             x = lin[i];
             if (r.temperature > 0.0f) x = __fdiv_rn(x, r.temperature);
-            kill = st.suppress[i] != 0;
+            kill = sup[i] != 0;
             if (r.suppress_blank && r.is_initial && (i == st.token_eot || i == st.token_space)) kill = true;
             if (r.no_timestamps && i >= beg) kill = true;
         }

@@ -98,6 +98,9 @@ struct SamplerRow {
     int   work_slot;       // which [3][V] work area (logits, logprobs, probs) to use
     int   prefiltered;     // 1: the work area already holds the logits after temperature, the static suppressions of wc:6187-6224 and
                            // logits_filter_callback (done on the host); continue from the rules that follow the callback
+    int   pad0;
+    const uint8_t * suppress;       // per-row masks (jobs with different suppress rules may share a launch); null: SamplerStatic's
+    const uint8_t * suppress_post;
 };
 struct SamplerOut {
     int   id, tid;
