@@ -100,7 +100,8 @@ def prod_lib():
     """The product library.  Must exist: there is no fallback of any kind."""
     lib = api.load_library()
     declare(lib, _B200_SIGS)
-    api.install_quiet_logging(lib)
+    if not os.environ.get("WB200_TEST_LOG"):   # WB200_TEST_LOG=1: leave the library's stderr logging on (debugging a failure)
+        api.install_quiet_logging(lib)
     return lib
 
 

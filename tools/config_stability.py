@@ -1,0 +1,38 @@
+#!/usr/bin/env python
+"""ISA-stability scan for the BASELINE.json config tests: runs (arch, recipe, strategy) on a range of clip seeds through the
+reference's AVX2 and -march=native builds and prints the seeds on which both builds return the same transcript.
+Usage: python tools/config_stability.py <arch> <rich|base> <greedy|beam5> <seed0> <n> [seconds] [dtw_preset]"""
+import sys
+import time
+
+sys.path.insert(0, "."); sys.path.insert(0, "tests")
+import conftest as cf  # noqa: E402
+from whisper_rust_b200 import (DtwModelPreset, DtwParameters, FullParams, SamplingStrategy, WhisperContext, WhisperContextParameters, api,  # noqa: E402
+                               synth)
+
+arch, rname, strat, seed0, n = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5])
+seconds = float(sys.argv[6]) if len(sys.argv) > 6 else 30.0
+preset = getattr(DtwModelPreset, sys.argv[7]) if len(sys.argv) > 7 else None
+recipe = synth.InitRecipe(te_std=0.2, pe_std=0.3, gain=3.0, ts_scale=1.6) if rname == "rich" else synth.InitRecipe(te_std=0.2)
+blob = synth.model_bytes(arch, recipe)
+res = {}
+for name, path in (("avx2", cf.ORACLE_LIB), ("native", cf.ORACLE_LIB.with_name("libwhisper_ref_native.so"))):
+    lib = cf.declare(api.load_library(path), cf._PROBE_SIGS)
+    api.install_quiet_logging(lib)
+    dtw = DtwParameters(preset=preset) if preset is not None else None
+    ctx = WhisperContext.new_from_buffer_with_params(blob, WhisperContextParameters(use_gpu=False, dtw_parameters=dtw), lib=lib)
+    st = ctx.create_state()
+    for seed in range(seed0, seed0 + n):
+        if strat == "beam5":
+            p = FullParams(lib, SamplingStrategy.BEAM_SEARCH, beam_size=5)
+        else:
+            p = FullParams(lib, SamplingStrategy.GREEDY, best_of=1)
+        p.set_n_threads(8).set_language("en").set_temperature_inc(0.0)
+        t0 = time.time()
+        assert st.full(p, synth.synth_audio(seconds, seed=seed)) == 0
+        segs = st.segments()
+        res[(name, seed)] = [(s.t0, s.t1, [t["id"] for t in s.tokens], [int(t["t_dtw"]) for t in s.tokens]) for s in segs]
+        print(name, seed, len(segs), sum(len(s.tokens) for s in segs), f"{time.time()-t0:.1f}s", flush=True)
+    st.free(); ctx.free()
+stable = [s for s in range(seed0, seed0 + n) if res[("avx2", s)] == res[("native", s)]]
+print("STABLE seeds:", stable)

@@ -23,3 +23,17 @@ for line in open(sys.argv[1]):
         l = d["lanes"][0]
         for i in range(int(sys.argv[2])):
             print(l["names"][i], (l["t_ns"][i] - t0) / 1e3)
+    # ---- concurrency of the K/V stream across lanes: a lane's cross interval = [its cross stamp, its next kernel's stamp)
+    iv = []
+    for l in lanes:
+        t, names = l["t_ns"], l["names"]
+        iv += [(t[i], t[i + 1]) for i in range(len(t) - 1) if names[i] == "cross"]
+    if len(lanes) > 1 and iv:
+        lo = max(l["t_ns"][0] for l in lanes); hi = min(l["t_ns"][-1] for l in lanes)   # window in which every lane is mid-step
+        ev = sorted([(max(a, lo), 1) for a, b in iv if b > lo and a < hi] + [(min(b, hi), -1) for a, b in iv if b > lo and a < hi])
+        occ = defaultdict(float); cur = 0; prev = lo
+        for t, dlt in ev:
+            occ[cur] += t - prev; prev = t; cur += dlt
+        occ[cur] += hi - prev
+        tot = max(1.0, float(hi - lo))
+        print(f"  common window {tot/1e3:.1f}us; lanes inside cross_attn_step at once: " + "  ".join(f"{k}:{v/tot:.3f}" for k, v in sorted(occ.items())))

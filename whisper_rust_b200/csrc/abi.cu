@@ -728,6 +728,16 @@ int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int window, floa
     }
     return n;
 }
+int64_t whisper_b200_test_conv_stem(struct whisper_context * ctx, struct whisper_state * state, int mel_offset, float * dst, int64_t cap) {
+    WB_TRY
+    if (!ctx || !state) return -1;
+    const int T = state->exp_n_audio_ctx > 0 ? state->exp_n_audio_ctx : ctx->model.hp.n_audio_ctx;
+    const int64_t n = (int64_t) T * ctx->model.hp.n_audio_state;
+    if (!dst || cap < n) return n;
+    bool ok = false;
+    return sched_run(ctx, [&] { ok = stage_conv_probe(*ctx, state, mel_offset, dst, cap); }) && ok ? n : -1;
+    WB_CATCH(-1)
+}
 int64_t whisper_b200_get_kv_cross(struct whisper_state * state, uint16_t * dst, int64_t cap) {
     if (!state || !state->ctx || state->cross_T <= 0) return -1;
     const auto & hp = state->ctx->model.hp;

@@ -352,7 +352,8 @@ static bool ensure_dec_ws(Context & ctx, int rows, int logit_rows, int max_cells
     ws.x = (float *) (ws.base + o_x); ws.xa = (__half *) (ws.base + o_xa); ws.qkv = (__half *) (ws.base + o_qkv);
     ws.q = (__half *) (ws.base + o_q); ws.att = (__half *) (ws.base + o_att); ws.hb = (__half *) (ws.base + o_hb);
     ws.logits = (float *) (ws.base + o_lg); ws.samp_work = (float *) (ws.base + o_sw); ws.d_cells = (int *) (ws.base + o_cells);
-    ws.stage_bytes = (size_t) R * (8 + sizeof(SelfKvRow) + sizeof(CrossKvRow) + sizeof(SamplerRow) + (size_t) MC * 4) + 4096;
+    // a multiple of 16: the sampler rows sit at the END of the block (stage_sample) and hold pointers (8-byte aligned loads)
+    ws.stage_bytes = (((size_t) R * (8 + sizeof(SelfKvRow) + sizeof(CrossKvRow) + sizeof(SamplerRow) + (size_t) MC * 4) + 4096) + 15) & ~(size_t) 15;
     WB_CUDA_OK(cudaMallocHost((void **) &ws.h_stage, ws.stage_bytes));
     WB_CUDA_OK(cudaMalloc((void **) &ws.d_stage, ws.stage_bytes));
     WB_CUDA_OK(cudaMallocHost((void **) &ws.h_out, (size_t) RL * sizeof(SamplerOut)));
@@ -436,13 +437,13 @@ static inline GemmEpilogue epi_row(void * out, bool f16, int64_t ldo) {
     return e;
 }
 
-static bool encode_chunk(Context & ctx, State * const * states, const int * mel_offsets, int W, int T) {
+// E1 (wc:1994-2054, 2106-2107): the mel slice of every window through the two convolutions into the residual stream ws.x
+static bool conv_stem(Context & ctx, State * const * states, const int * mel_offsets, int W, int T, bool add_pos_emb) {
     const Model & m = ctx.model;
     const auto & hp = m.hp;
-    const int S = hp.n_audio_state, H = hp.n_audio_head, L = hp.n_audio_layer, Lt = hp.n_text_layer;
-    if (!ensure_enc_ws(ctx, W, T)) return false;
+    const int S = hp.n_audio_state;
     EncWorkspace & ws = ctx.enc_ws;
-    const int Tpad = ws.Tpad, R = W * T, F = 2 * T;  // F mel frames per window
+    const int F = 2 * T;  // F mel frames per window
     g_prof_gemm_cat = PC_GEMM_ENC;
     cudaStream_t s = ctx.stream;
 
@@ -473,10 +474,37 @@ static bool encode_chunk(Context & ctx, State * const * states, const int * mel_
         e.out_batch_stride = (int64_t) T * S;
         e.bias = m.conv2_b;
         e.gelu_table = m.gelu_table;
-        e.res = m.e_pe;
-        e.ldr = S;
+        if (add_pos_emb) {
+            e.res = m.e_pe;
+            e.ldr = S;
+        }
         if (!gemm_f16_tc(A, B, T, S, S, W, e, 0, s, &taps)) return false;
     }
+    return true;
+}
+
+// test probe (whisper_b200_test_conv_stem): the conv stem alone, WITHOUT the positional embedding = the reference's embd_conv
+bool stage_conv_probe(Context & ctx, State * st, int mel_offset, float * dst, int64_t cap) {
+    WB_CUDA_OK(cudaSetDevice(ctx.model.device));
+    const int T = st->exp_n_audio_ctx > 0 ? st->exp_n_audio_ctx : ctx.model.hp.n_audio_ctx;
+    const int64_t n = (int64_t) T * ctx.model.hp.n_audio_state;
+    if (cap < n) return false;
+    if (!ensure_enc_ws(ctx, 1, T) || !conv_stem(ctx, &st, &mel_offset, 1, T, false)) return false;
+    WB_CUDA_OK(cudaMemcpyAsync(dst, ctx.enc_ws.x, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx.stream));
+    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    return true;
+}
+
+static bool encode_chunk(Context & ctx, State * const * states, const int * mel_offsets, int W, int T) {
+    const Model & m = ctx.model;
+    const auto & hp = m.hp;
+    const int S = hp.n_audio_state, H = hp.n_audio_head, L = hp.n_audio_layer, Lt = hp.n_text_layer;
+    if (!ensure_enc_ws(ctx, W, T)) return false;
+    EncWorkspace & ws = ctx.enc_ws;
+    const int Tpad = ws.Tpad, R = W * T;
+    g_prof_gemm_cat = PC_GEMM_ENC;
+    cudaStream_t s = ctx.stream;
+    if (!conv_stem(ctx, states, mel_offsets, W, T, true)) return false;
     // E2: encoder blocks (wc:2116-2255)
     const float kq_scale = 1.0f / sqrtf((float) 64);
     for (int il = 0; il < L; ++il) {

@@ -196,6 +196,7 @@ bool stage_set_mel(State & st, const float * data, int n_len, int n_mel);
 bool stage_get_mel(State & st, std::vector<float> & out);
 // Encodes one window of each listed state (mel offsets per state) as one batch, then fills their cross caches.
 bool stage_encode(Context & ctx, State * const * states, const int * mel_offsets, int n_states);
+bool stage_conv_probe(Context & ctx, State * st, int mel_offset, float * dst, int64_t cap);  // E1 alone, host dst [T][S]
 
 struct BatchRow {
     State * st;
