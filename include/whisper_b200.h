@@ -23,6 +23,18 @@ extern "C" {
 WHISPER_API int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
                                         struct whisper_full_params params, const float * const * samples, const int * n_samples);
 
+/* Harness for the unchanged API's threading contract: one host thread per state, each calling whisper_full_with_state(ctx, states[i],
+ * params, samples[i], n_samples[i]) (what a Rust caller's thread pool does; rs/whisper_state.rs:19-21).  Returns the first non-zero code. */
+WHISPER_API int whisper_b200_full_threads(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
+                                          struct whisper_full_params params, const float * const * samples, const int * n_samples);
+
+/* The same harness as a stream: thread i transcribes samples[r * n_states + i], r = 0 .. rounds-1, back to back on states[i] (no barrier
+ * between rounds; the scheduler admits a thread's next clip while other clips are still decoding).  read_back != 0: every call's result is
+ * read through the public accessors; *bytes_read (optional) receives the bytes read. */
+WHISPER_API int whisper_b200_full_stream(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
+                                         struct whisper_full_params params, const float * const * samples, const int * n_samples,
+                                         int rounds, int read_back, uint64_t * bytes_read);
+
 /* Batched stage entry points (same contracts as whisper_encode_with_state / whisper_decode_with_state, wc:3933-3971). */
 WHISPER_API int whisper_b200_encode_batch(struct whisper_context * ctx, struct whisper_state ** states, const int * offsets, int n_states);
 /* one new token per state at position n_past[i]; logits readable through whisper_get_logits_from_state */

@@ -13,7 +13,11 @@ from whisper_rust_b200 import (DtwModelPreset, DtwParameters, FullParams, Sampli
 arch, rname, strat, seed0, n = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5])
 seconds = float(sys.argv[6]) if len(sys.argv) > 6 else 30.0
 preset = getattr(DtwModelPreset, sys.argv[7]) if len(sys.argv) > 7 else None
-recipe = synth.InitRecipe(te_std=0.2, pe_std=0.3, gain=3.0, ts_scale=1.6) if rname == "rich" else synth.InitRecipe(te_std=0.2)
+if rname.startswith("r:"):   # r:<te_std>:<gain>:<ts_scale>
+    te, gain, ts = (float(x) for x in rname.split(":")[1:4])
+    recipe = synth.InitRecipe(te_std=te, pe_std=0.3, gain=gain, ts_scale=ts)
+else:
+    recipe = synth.InitRecipe(te_std=0.2, pe_std=0.3, gain=3.0, ts_scale=1.6) if rname == "rich" else synth.InitRecipe(te_std=0.2)
 blob = synth.model_bytes(arch, recipe)
 res = {}
 for name, path in (("avx2", cf.ORACLE_LIB), ("native", cf.ORACLE_LIB.with_name("libwhisper_ref_native.so"))):
@@ -35,4 +39,10 @@ for name, path in (("avx2", cf.ORACLE_LIB), ("native", cf.ORACLE_LIB.with_name("
         print(name, seed, len(segs), sum(len(s.tokens) for s in segs), f"{time.time()-t0:.1f}s", flush=True)
     st.free(); ctx.free()
 stable = [s for s in range(seed0, seed0 + n) if res[("avx2", s)] == res[("native", s)]]
-print("STABLE seeds:", stable)
+ids_only = lambda r: [(a, b, c) for a, b, c, d in r]
+stable_ids = [s for s in range(seed0, seed0 + n) if ids_only(res[("avx2", s)]) == ids_only(res[("native", s)])]
+for s in stable_ids:
+    if s not in stable:
+        da = [x for seg in res[("avx2", s)] for x in seg[3]]; db = [x for seg in res[("native", s)] for x in seg[3]]
+        print("seed", s, "ids equal, t_dtw differs at", sum(1 for x, y in zip(da, db) if x != y), "of", len(da), "max |d|", max(abs(x - y) for x, y in zip(da, db)))
+print("STABLE seeds:", stable, " ids/times stable:", stable_ids)

@@ -9,3 +9,14 @@ run() { # tag, env...
   echo "== $tag exit $? $(python -c "import json;d=json.load(open('$OUT/bench_$tag.json'));print(d['ms_per_step'], d['phase_ms_per_step_host_clock']['decode_step'])" 2>&1)"
   python tools/trace_summary.py $OUT/trace_$tag.jsonl | tail -${TAILN:-4}
 }
+for cfg in ${CFGS:-"lanes4"}; do
+  case $cfg in
+    lanes4) run lanes4 WB200_LANES=4 ;;
+    lanes2) run lanes2 WB200_LANES=2 ;;
+    lanes1) run lanes1 WB200_LANES=1 ;;
+    lanes4_nopdl) run lanes4_nopdl WB200_LANES=4 WB200_NO_PDL=1 ;;
+    lanes3) run lanes3 WB200_LANES=3 ;;
+    lanes5) run lanes5 WB200_LANES=5 ;;
+    lanes6) run lanes6 WB200_LANES=6 ;;
+  esac
+done

@@ -24,7 +24,7 @@ stable = []
 for name in (sys.argv[1:] or list(oc.CASES)):
     res = {}
     for b, lib in libs.items():
-        ctx = WhisperContext.new_from_buffer_with_params(cf.model_blob("mini", oc.RICH), WhisperContextParameters(use_gpu=False), lib=lib)
+        ctx = WhisperContext.new_from_buffer_with_params(cf.model_blob(*oc.model_of(name)), WhisperContextParameters(use_gpu=False), lib=lib)
         res[b] = key(oc.run_case(name, lib, ctx))
         ctx.free()
     same = res["avx2"] == res["native"]

@@ -10,7 +10,8 @@ for line in open(sys.argv[1]):
         subs = l.get("sub") or [0] * len(l["t_ns"])
         for sub in sorted(set(subs)):
             idx = [i for i, x in enumerate(subs) if x == sub]
-            lanes.append({"lane": f"{l['lane']}.{sub}", "n": l["n"], "t_ns": [l["t_ns"][i] for i in idx], "names": [l["names"][i] for i in idx]})
+            lanes.append({"lane": f"{l['lane']}.{sub}", "n": l["n"], "t_ns": [l["t_ns"][i] for i in idx], "names": [l["names"][i] for i in idx],
+                          "t_end_ns": [l["t_end_ns"][i] for i in idx] if "t_end_ns" in l else None})
     for l in lanes:
         t, names = l["t_ns"], l["names"]
         dur = defaultdict(float); cnt = defaultdict(int)
@@ -19,6 +20,13 @@ for line in open(sys.argv[1]):
         tot = (t[-1] - t[0]) / 1e3
         print(f"lane {l['lane']} n={l['n']} start={(t[0]-t0)/1e3:9.1f}us span={tot:9.1f}us  " +
               "  ".join(f"{k}:{dur[k]/cnt[k]:.1f}x{cnt[k]}" for k in sorted(dur)))
+        te = l.get("t_end_ns")
+        if te:   # block 0's own run time (start stamp -> its exit) and what follows it until the next kernel's start stamp
+            run = defaultdict(float); gap = defaultdict(float)
+            for i in range(len(t) - 1):
+                if te[i] >= t[i]:
+                    run[names[i]] += (te[i] - t[i]) / 1e3; gap[names[i]] += (t[i + 1] - te[i]) / 1e3
+            print("      block-0 run / gap to next start:  " + "  ".join(f"{k}:{run[k]/cnt[k]:.1f}/{gap[k]/cnt[k]:.1f}" for k in sorted(run)))
     if len(sys.argv) > 2:
         l = d["lanes"][0]
         for i in range(int(sys.argv[2])):

@@ -555,6 +555,69 @@ int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state *
     WB_CATCH(-1)
 }
 
+// Host-side harness for the drop-in threading contract (rs/whisper_state.rs:19-21: states are Send+Sync): one std::thread per
+// state, each making an ordinary whisper_full_with_state call on the shared context, exactly what a Rust caller's thread pool does.
+// Nothing here is batched by the caller; the batching happens in the library's scheduler.
+int whisper_b200_full_threads(struct whisper_context * ctx, struct whisper_state ** states, int n_states, struct whisper_full_params params,
+                              const float * const * samples, const int * n_samples) {
+    WB_TRY
+    if (!ctx || !states || n_states <= 0 || !samples || !n_samples) return -1;
+    std::vector<int> rc((size_t) n_states, 0);
+    std::vector<std::thread> th;
+    th.reserve((size_t) n_states);
+    for (int i = 0; i < n_states; ++i)
+        th.emplace_back([&, i] { rc[(size_t) i] = whisper_full_with_state(ctx, states[i], params, samples[i], n_samples[i]); });
+    for (auto & t : th) t.join();
+    for (int r : rc)
+        if (r != 0) return r;
+    return 0;
+    WB_CATCH(-1)
+}
+
+// The same harness as a stream of work: thread i transcribes samples[r * n_states + i] for r = 0 .. rounds-1 back to back on its own
+// state (a worker thread of a server draining its queue).  There is no barrier between rounds: a thread submits its next clip as soon
+// as its previous call returns, and the scheduler admits it while other threads' clips are still decoding.  With read_back != 0 every
+// call's result is read through the public accessors (segments, times, text, token data) like a caller would; *bytes_read sums them.
+int whisper_b200_full_stream(struct whisper_context * ctx, struct whisper_state ** states, int n_states, struct whisper_full_params params,
+                             const float * const * samples, const int * n_samples, int rounds, int read_back, uint64_t * bytes_read) {
+    WB_TRY
+    if (!ctx || !states || n_states <= 0 || !samples || !n_samples || rounds <= 0) return -1;
+    std::vector<int> rc((size_t) n_states, 0);
+    std::vector<uint64_t> nb((size_t) n_states, 0);
+    std::vector<std::thread> th;
+    th.reserve((size_t) n_states);
+    for (int i = 0; i < n_states; ++i)
+        th.emplace_back([&, i] {
+            whisper_state * st = states[i];
+            for (int r = 0; r < rounds && rc[(size_t) i] == 0; ++r) {
+                const size_t k = (size_t) r * n_states + i;
+                rc[(size_t) i] = whisper_full_with_state(ctx, st, params, samples[k], n_samples[k]);
+                if (!read_back || rc[(size_t) i] != 0) continue;
+                const int ns = whisper_full_n_segments_from_state(st);
+                for (int sgi = 0; sgi < ns; ++sgi) {
+                    const char * txt = whisper_full_get_segment_text_from_state(st, sgi);
+                    nb[(size_t) i] += 16 + (txt ? strlen(txt) : 0);
+                    (void) whisper_full_get_segment_t0_from_state(st, sgi);
+                    (void) whisper_full_get_segment_t1_from_state(st, sgi);
+                    const int nt = whisper_full_n_tokens_from_state(st, sgi);
+                    for (int t = 0; t < nt; ++t) {
+                        const whisper_token_data td = whisper_full_get_token_data_from_state(st, sgi, t);
+                        nb[(size_t) i] += sizeof(td) + (td.id < 0 ? 1 : 0);
+                    }
+                }
+            }
+        });
+    for (auto & t : th) t.join();
+    if (bytes_read) {
+        *bytes_read = 0;
+        for (uint64_t b : nb) *bytes_read += b;
+    }
+    for (int r : rc)
+        if (r != 0) return r;
+    return 0;
+    WB_CATCH(-1)
+}
+
 // whisper_full_parallel (wc:7736-7864): equal sample spans, one state per span — here the spans advance as ONE batch on
 // the device instead of one CPU thread each; the merge rule (time offsets, clamping, append order) is the reference's.
 int whisper_full_parallel(struct whisper_context * ctx, struct whisper_full_params params, const float * samples, int n_samples, int n_processors) {

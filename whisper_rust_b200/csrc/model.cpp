@@ -76,6 +76,85 @@ static inline uint16_t f2h(float f) {
 
 enum class Kind { F32_VEC, F16_MAT, CONV1, CONV2 };
 
+// ---- quantised ggml tensor types (ftype -> wtype: wc:1567-1577; block layouts: ggml/src/ggml-common.h, dequantize_row_*:
+// ggml/src/ggml-quants.c).  The B200 path computes in f16 x f16 -> f32: a quantised matrix is expanded ONCE at load,
+// x = q * d (+ m) evaluated in f32 like dequantize_row_*, then rounded to f16.  (The reference instead keeps the blocks and
+// quantises the ACTIVATIONS to q8_0/q8_1 inside vec_dot, so agreement with it on such checkpoints is tolerance-level.)
+enum : int { GT_F32 = 0, GT_F16 = 1, GT_Q4_0 = 2, GT_Q4_1 = 3, GT_Q5_0 = 6, GT_Q5_1 = 7, GT_Q8_0 = 8 };
+static constexpr int QK = 32;   // elements per block, all five legacy types
+
+static int ftype_to_wtype(int ftype) {  // ggml_ftype_to_ggml_type (ggml.c); -1: not supported here
+    switch (ftype) {
+        case 0: return GT_F32;
+        case 1: return GT_F16;
+        case 2: return GT_Q4_0;
+        case 3: return GT_Q4_1;
+        case 7: return GT_Q8_0;
+        case 8: return GT_Q5_0;
+        case 9: return GT_Q5_1;
+        default: return -1;   // 4 (Q4_1_SOME_F16) is rejected by ggml itself; 10+ are the 256-wide K-quants / IQ types
+    }
+}
+static size_t quant_block_bytes(int t) {
+    switch (t) {
+        case GT_Q4_0: return 2 + 16;
+        case GT_Q4_1: return 4 + 16;
+        case GT_Q5_0: return 2 + 4 + 16;
+        case GT_Q5_1: return 4 + 4 + 16;
+        case GT_Q8_0: return 2 + 32;
+        default: return 0;
+    }
+}
+static void dequantize_blocks(int t, const uint8_t * src, int64_t n, float * dst) {
+    const int64_t nb = n / QK;
+    const size_t bs = quant_block_bytes(t);
+    for (int64_t b = 0; b < nb; ++b) {
+        const uint8_t * p = src + (size_t) b * bs;
+        float * y = dst + b * QK;
+        uint16_t dh, mh = 0;
+        memcpy(&dh, p, 2);
+        const float d = h2f(dh);
+        if (t == GT_Q8_0) {
+            const int8_t * q = (const int8_t *) (p + 2);
+            for (int j = 0; j < QK; ++j) y[j] = q[j] * d;
+        } else if (t == GT_Q4_0) {
+            const uint8_t * q = p + 2;
+            for (int j = 0; j < QK / 2; ++j) {
+                y[j] = ((int) (q[j] & 0x0F) - 8) * d;
+                y[j + QK / 2] = ((int) (q[j] >> 4) - 8) * d;
+            }
+        } else if (t == GT_Q4_1) {
+            memcpy(&mh, p + 2, 2);
+            const float mn = h2f(mh);
+            const uint8_t * q = p + 4;
+            for (int j = 0; j < QK / 2; ++j) {
+                y[j] = (q[j] & 0x0F) * d + mn;
+                y[j + QK / 2] = (q[j] >> 4) * d + mn;
+            }
+        } else if (t == GT_Q5_0) {
+            uint32_t qh;
+            memcpy(&qh, p + 2, 4);
+            const uint8_t * q = p + 6;
+            for (int j = 0; j < QK / 2; ++j) {
+                const uint8_t xh0 = ((qh >> (j + 0)) << 4) & 0x10, xh1 = (qh >> (j + 12)) & 0x10;
+                y[j] = ((int) ((q[j] & 0x0F) | xh0) - 16) * d;
+                y[j + QK / 2] = ((int) ((q[j] >> 4) | xh1) - 16) * d;
+            }
+        } else {  // GT_Q5_1
+            memcpy(&mh, p + 2, 2);
+            const float mn = h2f(mh);
+            uint32_t qh;
+            memcpy(&qh, p + 4, 4);
+            const uint8_t * q = p + 8;
+            for (int j = 0; j < QK / 2; ++j) {
+                const uint8_t xh0 = ((qh >> (j + 0)) << 4) & 0x10, xh1 = (qh >> (j + 12)) & 0x10;
+                y[j] = ((q[j] & 0x0F) | xh0) * d + mn;
+                y[j + QK / 2] = ((q[j] >> 4) | xh1) * d + mn;
+            }
+        }
+    }
+}
+
 struct Dest {
     Kind kind;
     void * ptr;          // device destination
@@ -117,9 +196,10 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     const int qntvr = hp.ftype / 1000;
     hp.ftype %= 1000;
     (void) qntvr;
-    if (hp.ftype != 0 && hp.ftype != 1) {
-        log_error("%s: unsupported model ftype %d: this build runs f32/f16 checkpoints only (quantised ggml types are not "
-                  "on the B200 path)\n", __func__, hp.ftype);
+    const int wtype = ftype_to_wtype(hp.ftype);  // wc:1567-1577
+    if (wtype < 0) {
+        log_error("%s: invalid model (bad ftype value %d): supported are f32, f16, q4_0, q4_1, q5_0, q5_1, q8_0 (the 256-wide K-quants "
+                  "are not expanded by this loader)\n", __func__, hp.ftype);
         return false;
     }
     const int S = hp.n_audio_state, H = hp.n_audio_head, T = hp.n_audio_ctx, M = hp.n_mels, V = hp.n_vocab;
@@ -341,6 +421,7 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     // ---------------- stream the tensor records (wc:1887-1955) ----------------
     std::vector<uint8_t> buf;
     std::vector<uint16_t> re;
+    std::vector<float> deq;
     size_t total = 0;
     m.n_loaded = 0;
     while (true) {
@@ -375,20 +456,35 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
                       ne[0], ne[1], ne[2], d.ne[0], d.ne[1], d.ne[2]);
             return false;
         }
-        if (ttype != 0 && ttype != 1) {
+        const size_t qbs = quant_block_bytes(ttype);
+        if (ttype != GT_F32 && ttype != GT_F16 && qbs == 0) {
             log_error("%s: tensor '%s' has unsupported type %d\n", __func__, name.c_str(), ttype);
             return false;
         }
         const bool want_f16 = d.kind != Kind::F32_VEC;
-        if (!want_f16 && ttype != 0) {
+        if (!want_f16 && ttype != GT_F32) {
             log_error("%s: tensor '%s' has wrong size in model file: expected f32 data\n", __func__, name.c_str());
             return false;
         }
-        const size_t bpe = ttype == 1 ? 2 : 4;
-        buf.resize((size_t) nelements * bpe);
+        if (qbs != 0 && (d.kind != Kind::F16_MAT || ttype != wtype || (ne[0] % QK) != 0)) {
+            // the reference sizes every matrix by the file's wtype and the conv kernels by f16 (wc:1696): anything else is
+            // "wrong size in model file" there too
+            log_error("%s: tensor '%s' has wrong size in model file (type %d, model wtype %d)\n", __func__, name.c_str(), ttype, wtype);
+            return false;
+        }
+        const size_t file_bytes = qbs != 0 ? (size_t) (nelements / QK) * qbs : (size_t) nelements * (ttype == GT_F16 ? 2 : 4);
+        buf.resize(file_bytes);
         if (!rd.read(buf.data(), buf.size())) {
             log_error("%s: tensor '%s' is truncated\n", __func__, name.c_str());
             return false;
+        }
+        total += file_bytes;
+        if (qbs != 0) {  // expand the blocks to f32 (dequantize_row_*), then treat the tensor like an f32 checkpoint's
+            deq.resize((size_t) nelements);
+            dequantize_blocks(ttype, buf.data(), nelements, deq.data());
+            buf.resize((size_t) nelements * 4);
+            memcpy(buf.data(), deq.data(), buf.size());
+            ttype = GT_F32;
         }
         const void * src = buf.data();
         size_t nbytes = buf.size();
@@ -416,7 +512,6 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
         } else {
             WB_CUDA_OK(cudaMemcpy(d.ptr, src, nbytes, cudaMemcpyHostToDevice));
         }
-        total += nbytes;
         m.n_loaded++;
     }
     log_msg(GGML_LOG_LEVEL_INFO, "%s: model size    = %7.2f MB (%d tensors, device arena %.2f MB)\n", __func__, total / 1e6, m.n_loaded,

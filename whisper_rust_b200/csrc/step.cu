@@ -34,7 +34,23 @@ __device__ __forceinline__ void trace_stamp(unsigned long long * slot) {
         *slot = t;
     }
 }
+// second stamp of a kernel's slot pair: block 0 is about to exit (its own work is done; other blocks may still run)
+__device__ __forceinline__ void trace_stamp_end(unsigned long long * slot) {
+    if (slot != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+        slot[1] = t;
+    }
+}
 
+// Register budgets (minimum resident CTAs per SM in __launch_bounds__): with two persistent cross-attention CTAs resident (2 x 288 threads x 80 registers = 46 K of the SM's
+// 64 K) the short kernels of the OTHER decode lanes share what is left; capping their registers decides how many of their CTAs fit.
+#ifndef WB_SELF_MIN_CTAS
+#define WB_SELF_MIN_CTAS 8
+#endif
+#ifndef WB_LN_MIN_CTAS
+#define WB_LN_MIN_CTAS 5
+#endif
 struct WsArgs {
     unsigned long long * trace;
     int n, n_pad, N_out;
@@ -181,6 +197,7 @@ gemm_wstream_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         tc_fence_before();
     }
     __syncthreads();
+    if (threadIdx.x == 0) trace_stamp_end(a.trace);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc_rt(tmem_base, a.tmem_cols);
@@ -393,6 +410,7 @@ gemm_wcluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
     }
     __syncwarp();
     cluster_sync_all();  // no CTA may exit (and release its shared memory) while a peer is still reading it
+    if (threadIdx.x == 0) trace_stamp_end(a.trace);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc_rt(tmem_base, a.tmem_cols);
@@ -417,7 +435,9 @@ static unsigned long long * trace_slot(const char * name) {
     if (!g_trace_next) return nullptr;
     if (g_trace_names) g_trace_names->push_back(name);
     if (g_trace_subs) g_trace_subs->push_back(g_trace_sub);
-    return g_trace_next++;
+    unsigned long long * p = g_trace_next;
+    g_trace_next += 2;  // (start, end of block 0)
+    return p;
 }  // cudaLaunchAttributePriority of the next launches (0: none; set around issue_step when lanes run)
 
 // Tuning of the kernels that share the SMs when several decode lanes are in flight (set by stage_step_launch):
@@ -639,7 +659,7 @@ __device__ __forceinline__ double block_sum_double(double v, double * red /*[8]*
     return r;
 }
 
-__global__ void __launch_bounds__(LN_THREADS)
+__global__ void __launch_bounds__(LN_THREADS, WB_LN_MIN_CTAS)
 ln_reduce_kernel(LnArgs a) {
     __shared__ double red[8];
     pdl_launch_dependents();
@@ -704,6 +724,7 @@ ln_reduce_kernel(LnArgs a) {
             a.xa_out[(int64_t) row * S + i] = __float2half_rn(y);
         }
     }
+    if (tid == 0) trace_stamp_end(a.trace);
 }
 
 // =============================================================================================
@@ -724,7 +745,7 @@ struct SelfArgs {
     const __half * qkv16;   // alternative to partial: finished f16 Q|K|V [n][3S] (bias and D^-1/4 scale applied by the GEMM)
 };
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, WB_SELF_MIN_CTAS)
 self_attn_step_kernel(SelfArgs a) {
     extern __shared__ float s_sc[];
     __shared__ float s_q[64];
@@ -823,6 +844,7 @@ self_attn_step_kernel(SelfArgs a) {
         for (int g = 0; g < 16; ++g) o += s_pv[g][tid];
         a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
     }
+    if (tid == 0) trace_stamp_end(a.trace);
 }
 
 // =============================================================================================
@@ -1071,6 +1093,7 @@ cross_attn_step_kernel(CrossArgs a) {
             a.out[(int64_t) j * S + h * 64 + tid] = __float2half_rn(o);
         }
     }
+    if (tid == 0) trace_stamp_end(a.trace);
 }
 
 static int xs_smem_bytes(int T, int stages) { return stages * XS_CHUNK_BYTES + ((T + 31) & ~31) * 4 + 2 * stages * 8 + 128 + 64; }
@@ -1430,14 +1453,20 @@ void step_trace_dump(Context & ctx) {
     for (int l = 0; l < MAX_LANES; ++l) {
         StepWs & ws = L.ws[l];
         if (!ws.d_trace || ws.trace_names.empty()) continue;
-        std::vector<unsigned long long> t(ws.trace_names.size());
-        if (cudaMemcpy(t.data(), ws.d_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) continue;
+        std::vector<unsigned long long> t2(2 * ws.trace_names.size()), t(ws.trace_names.size()), te(ws.trace_names.size());
+        if (cudaMemcpy(t2.data(), ws.d_trace, t2.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) continue;
+        for (size_t i = 0; i < t.size(); ++i) {
+            t[i] = t2[2 * i];
+            te[i] = t2[2 * i + 1];
+        }
         fprintf(f, "%s{\"lane\": %d, \"n\": %d, \"names\": [", first ? "" : ", ", l, ws.trace_n);
         for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s\"%s\"", i ? "," : "", ws.trace_names[i]);
         fprintf(f, "], \"sub\": [");
         for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s%d", i ? "," : "", i < ws.trace_subs.size() ? ws.trace_subs[i] : 0);
         fprintf(f, "], \"t_ns\": [");
         for (size_t i = 0; i < t.size(); ++i) fprintf(f, "%s%llu", i ? "," : "", t[i]);
+        fprintf(f, "], \"t_end_ns\": [");
+        for (size_t i = 0; i < te.size(); ++i) fprintf(f, "%s%llu", i ? "," : "", te[i]);
         fprintf(f, "]}");
         first = false;
     }

@@ -61,6 +61,10 @@ ARCHS = {
     # reduced shapes for fast CPU-side tests (same layer structure, D=64 heads)
     # (micro has 2 text layers, so the reference treats it as a first-release distilled model and forces no_timestamps,
     #  whisper.cpp:6956-6960; mini has 3 and keeps the timestamp logic live)
+    # large-v3-turbo: 32 encoder / 4 decoder layers (n_audio_layer != n_text_layer); "miniturbo" is its reduced-shape stand-in
+    "large-v3-turbo": Arch("large-v3-turbo", 51866, 1500, 1280, 20, 32, 448, 1280, 20, 4, 128),
+    "miniturbo": Arch("miniturbo", 51866, 1500, 192, 3, 5, 448, 192, 3, 3, 128),
+    "distil":   Arch("distil", 51865, 1500, 192, 3, 4, 448, 192, 3, 2, 80),
     "micro":    Arch("micro", 51865, 1500, 128, 2, 2, 448, 128, 2, 2, 80),
     "mini":     Arch("mini", 51865, 1500, 192, 3, 2, 448, 192, 3, 3, 80),
 }
@@ -157,7 +161,71 @@ class InitRecipe:
                             # sampler emit timestamps, hence several segments / windows per clip (test-design parameter)
 
 
-def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype: int = 1, with_tensors: bool = True) -> int:
+# ---- quantised checkpoints (examples/quantize: ggml_common_quantize_0 quantises the 2-D matrices, leaves the 3-D conv kernels f16 and
+# the 1-D / positional tensors f32).  Block layouts: ggml/src/ggml-common.h; the arithmetic follows quantize_row_*_ref (ggml-quants.c).
+FTYPE_TO_TTYPE = {2: 2, 3: 3, 7: 8, 8: 6, 9: 7}     # ggml_ftype -> ggml_type: q4_0, q4_1, q8_0, q5_0, q5_1
+
+
+def _quantize(x: np.ndarray, ttype: int) -> bytes:
+    """x: f32, size a multiple of 32 -> the ggml block stream of type ttype (2 q4_0, 6 q5_0, 8 q8_0)"""
+    b = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    nb = b.shape[0]
+    if ttype == 8:      # q8_0: d = amax / 127, q = round(x / d)   (quantize_row_q8_0_ref, ggml-quants.c:188-211)
+        amax = np.abs(b).max(axis=1)
+        d = (amax / np.float32(127)).astype(np.float32)
+        inv = np.where(d != 0, np.float32(1) / np.where(d != 0, d, 1), 0).astype(np.float32)
+        v = b * inv[:, None]
+        q = (np.sign(v) * np.floor(np.abs(v) + np.float32(0.5))).astype(np.int8)      # roundf: half away from zero
+        out = np.zeros((nb, 34), dtype=np.uint8)
+        out[:, 0:2] = d.astype("<f2").view(np.uint8).reshape(nb, 2)
+        out[:, 2:] = q.view(np.uint8)
+        return out.tobytes()
+    if ttype in (2, 6):  # q4_0 / q5_0: d = (value of largest magnitude) / -8 or -16   (ggml-quants.c:33-56, 99-141)
+        levels = 8 if ttype == 2 else 16
+        idx = np.abs(b).argmax(axis=1)
+        mx = b[np.arange(nb), idx]
+        d = (mx / np.float32(-levels)).astype(np.float32)
+        inv = np.where(d != 0, np.float32(1) / np.where(d != 0, d, 1), 0).astype(np.float32)
+        v = b * inv[:, None] + np.float32(levels + 0.5)
+        xi = np.minimum(2 * levels - 1, v.astype(np.int8).astype(np.int32)).astype(np.uint8)   # MIN(15|31, (int8_t)(x*id + 8.5|16.5))
+        lo, hi = xi[:, :16], xi[:, 16:]
+        qs = ((lo & 0x0F) | ((hi & 0x0F) << 4)).astype(np.uint8)
+        if ttype == 2:
+            out = np.zeros((nb, 18), dtype=np.uint8)
+            out[:, 0:2] = d.astype("<f2").view(np.uint8).reshape(nb, 2)
+            out[:, 2:] = qs
+            return out.tobytes()
+        sh = np.arange(16, dtype=np.uint32)
+        qh = (((lo.astype(np.uint32) & 0x10) >> 4) << sh).sum(axis=1, dtype=np.uint32) | \
+             (((hi.astype(np.uint32) & 0x10) >> 4) << (sh + 16)).sum(axis=1, dtype=np.uint32)
+        out = np.zeros((nb, 22), dtype=np.uint8)
+        out[:, 0:2] = d.astype("<f2").view(np.uint8).reshape(nb, 2)
+        out[:, 2:6] = qh.astype("<u4").view(np.uint8).reshape(nb, 4)
+        out[:, 6:] = qs
+        return out.tobytes()
+    raise ValueError(f"synthetic writer: ggml type {ttype} not implemented")
+
+
+def _dequantize(raw: bytes, ttype: int, n: int) -> np.ndarray:
+    """inverse of _quantize, evaluated in f32 like dequantize_row_* (ggml-quants.c)"""
+    bs = {2: 18, 6: 22, 8: 34}[ttype]
+    b = np.frombuffer(raw, dtype=np.uint8).reshape(-1, bs)
+    d = b[:, 0:2].copy().view("<f2").astype(np.float32)            # [nb][1]
+    if ttype == 8:
+        return (b[:, 2:].copy().view(np.int8).astype(np.float32) * d).reshape(n)
+    qs = b[:, (2 if ttype == 2 else 6):].astype(np.int32)
+    lo, hi = qs & 0x0F, qs >> 4
+    if ttype == 6:
+        qh = b[:, 2:6].copy().view("<u4").astype(np.uint32)        # [nb][1]
+        sh = np.arange(16, dtype=np.uint32)
+        lo = lo | (((qh >> sh) & 1) << 4).astype(np.int32)
+        hi = hi | (((qh >> (sh + 16)) & 1) << 4).astype(np.int32)
+    off = 8 if ttype == 2 else 16
+    return (np.concatenate([lo - off, hi - off], axis=1).astype(np.float32) * d).reshape(n)
+
+
+def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype: int = 1, with_tensors: bool = True,
+                expand_ftype: int | None = None) -> int:
     """Write a random-init model to `out` (path or binary file object). Returns bytes written.
 
     with_tensors=False writes the reference's own test convention: a header-only file with
@@ -196,13 +264,18 @@ def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype:
                     x *= recipe.te_std
                     if recipe.ts_scale != 1.0:
                         x[N_BASE_TOKENS + 107:] *= recipe.ts_scale
-                f16 = ftype == 1 and kind in ("w", "cw", "te")
-                data = x.astype("<f2" if f16 else "<f4")
+                if expand_ftype is not None and kind in ("w", "te"):
+                    # the f16 checkpoint a quantised one expands to: x = f16(dequantize(quantize(x))) (what the B200 loader keeps)
+                    qt0 = FTYPE_TO_TTYPE[expand_ftype]
+                    x = _dequantize(_quantize(x, qt0), qt0, n).reshape(shape)
+                f16 = (ftype == 1 and kind in ("w", "cw", "te")) or (ftype >= 2 and kind == "cw")
+                qt = FTYPE_TO_TTYPE[ftype] if ftype >= 2 and kind in ("w", "te") else None
+                payload = _quantize(x, qt) if qt is not None else x.astype("<f2" if f16 else "<f4").tobytes()
                 nm = name.encode()
-                f.write(struct.pack("<3i", len(shape), len(nm), 1 if f16 else 0))
+                f.write(struct.pack("<3i", len(shape), len(nm), qt if qt is not None else (1 if f16 else 0)))
                 f.write(struct.pack(f"<{len(shape)}i", *reversed(shape)))
                 f.write(nm)
-                f.write(data.tobytes())
+                f.write(payload)
         return f.tell() - n0
     finally:
         if own:
