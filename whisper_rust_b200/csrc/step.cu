@@ -549,7 +549,8 @@ static WcPlan wc_plan(int n, int N_out, int K) {
     p.kb_total = ceil_div(K, 64);
     p.n_pad    = (int) pad_to(std::max(n, 1), 16);
     // ~one CTA per SM, clusters of at most 8 (the portable limit), at least two k-blocks per CTA
-    int split = std::max(1, std::min(8, 148 / p.tiles));
+    static const int target_ctas = std::max(1, env_int("WB200_WC_CTAS", 148));  // tuning knob: fewer, longer-running CTAs per GEMM
+    int split = std::max(1, std::min(8, target_ctas / p.tiles));
     split = std::min(split, std::max(1, p.kb_total / 2));
     p.kb_per_split = ceil_div(p.kb_total, split);
     p.split        = ceil_div(p.kb_total, p.kb_per_split);
