@@ -1,16 +1,21 @@
 #!/usr/bin/env python
 """bench.py — RTFx (audio-seconds per second) of the transcription hot path, large-v3 greedy, on N B200s.
 
-One "step" = one pass of the whole path (PCM -> log-mel -> encoder -> greedy decode loop -> segments) over one batch
-of `--batch` independent 30 s shards per GPU, through whisper_b200_full_batch (the lock-step form of
-whisper_full_with_state).  Weak scaling: every rank processes its own batch; there is no collective on the math path.
+One "step" = one pass of the whole path (PCM -> log-mel -> encoder -> greedy decode loop -> segments) over one batch of `--batch`
+independent 30 s shards per GPU.  The shards go through the reference's own entry point: `--batch` host threads, one WhisperState each,
+every thread calling the unchanged whisper_full_with_state (`--api stream`, default: thread i transcribes shard i of step 0, 1, ...
+back to back; `--api threads`: the same with a join after every step; `--api batch`: the additive whisper_b200_full_batch).  The
+library's per-context scheduler turns the concurrent calls into batched device work.  Weak scaling: every rank processes its own
+batches; there is no collective on the math path.  `--workload clip` measures the strong-scaling form (one long clip sharded over the
+ranks, host gather inside the timed region).
 
   value : shards' PCM already resident in HBM when the timed region starts
-  e2e   : the same call with pinned HOST PCM (H2D inside the timed region) + reading every segment/token back
+  e2e   : the same calls with pinned HOST PCM (H2D inside the timed region) + reading every segment/token back through the accessors
   roofline : the dominant kernel category, timed in situ with CUDA events on the launching stream
-  cpu_baseline : the reference's own CPU engine (oracle/_ref) on a bounded sample, rank 0, N=1
+  cpu_baseline : the reference's own CPU engine (oracle/_ref, -march=native build) on a bounded sample, rank 0, N=1, with a
+                 token-by-token diff of its transcripts against the CUDA path's output of the timed region (`parity`)
 
-`--impl reference` times the reference CPU engine alone on the same config (one shard per step).
+`--impl reference` times the reference CPU engine alone on the same config (one shard per step, one thread per physical core).
 """
 from __future__ import annotations
 
@@ -205,8 +210,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="large-v3")
-    ap.add_argument("--batch", type=int, default=384, help="30 s shards per GPU per step: 4 decode lanes of 96 sequences; 384 sequences x "
-                    "330 MB of KV state = 127 GB of the 180 GB (B200 sweep in DESIGN.md section 7)")
+    ap.add_argument("--batch", type=int, default=448, help="30 s shards per GPU per step: 4 decode lanes of 112 sequences; 448 sequences x "
+                    "335 MB of KV state = 150 GB of the 180 GB (B200 sweep in DESIGN.md section 7: 384 -> 412 -> 448 = +1.4 % / +2.5 %)")
     ap.add_argument("--seconds", type=float, default=30.0)
     ap.add_argument("--workload", default="batch", choices=["batch", "clip"],
                     help="batch: --batch independent 30 s shards per GPU per step (weak scaling, the default the driver runs); clip: one "
@@ -215,9 +220,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the e2e pass, the other-API comparison and the small-batch quantities (tuning runs)")
     ap.add_argument("--parity-shards", type=int, default=8, help="shards of the last timed step the reference CPU engine re-transcribes")
-    ap.add_argument("--api", default="threads", choices=["threads", "batch", "stream"],
-                    help="threads: one host thread per state, each an unchanged whisper_full_with_state call (the library's scheduler batches "
-                         "them); batch: the additive whisper_b200_full_batch entry point")
+    ap.add_argument("--api", default="stream", choices=["threads", "batch", "stream"],
+                    help="stream (default): one host thread per state; thread i transcribes shard i of step 0, 1, ... back to back through the "
+                         "unchanged whisper_full_with_state (a server's worker threads draining their queues; the library's scheduler batches the "
+                         "calls); threads: the same with a join after every step; batch: the additive whisper_b200_full_batch entry point")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -469,7 +475,8 @@ def main():
             "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": B * n_samples * 4, "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": ms_e2e / args.steps},
             "api": {"timed": args.api,
-                    "note": "threads = one host thread per state calling the unchanged whisper_full_with_state; batch = whisper_b200_full_batch",
+                    "note": "stream / threads = one host thread per state calling the unchanged whisper_full_with_state (stream: no join between "
+                            "steps); batch = whisper_b200_full_batch; the second figure is the same workload through the other entry point",
                     args.api: value, other: audio_s_per_step * args.steps / (ms_other / 1e3)},
             "b1_latency_ms": small.get("1", {}).get("wall_ms"),
             "decode_ms_per_step_at_batch": {k: v["decode_ms_per_step"] for k, v in small.items()},

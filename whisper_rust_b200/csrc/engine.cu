@@ -331,7 +331,12 @@ static bool ensure_dec_ws(Context & ctx, int rows, int logit_rows, int max_cells
     if (ws.base && ws.rows >= rows && ws.logit_rows >= logit_rows && ws.max_cells >= max_cells) return true;
     const auto & hp = ctx.model.hp;
     const int S = hp.n_text_state, V = hp.n_vocab;
-    const int R = std::max(rows, ws.rows), RL = std::max(logit_rows, ws.logit_rows), MC = std::max(max_cells, ws.max_cells);
+    // Growing means cudaFree / cudaFreeHost / cudaHostAlloc on a process that holds ~150 GB of device memory and hundreds of pinned
+    // regions: measured 0.85 s for ONE regrow in the middle of a 448-state run (a second-window prompt with 101 carried-over tokens
+    // raised max_cells from 3 to 105).  So: start at the sizes the greedy path can reach (512 cells = one decoder's whole cache,
+    // wc:7101-7106) and grow geometrically.
+    auto grow = [](int need, int have, int floor_) { return need <= have ? have : std::max(std::max(need, floor_), have + have / 2); };
+    const int R = grow(rows, ws.rows, 64), RL = grow(logit_rows, ws.logit_rows, MAX_DECODERS), MC = grow(max_cells, ws.max_cells, 512);
     WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
     cudaFree(ws.base);
     if (ws.h_stage) cudaFreeHost(ws.h_stage);
@@ -367,7 +372,7 @@ static bool ensure_dec_ws(Context & ctx, int rows, int logit_rows, int max_cells
 // =============================================================================================
 // M1: mel
 // =============================================================================================
-bool stage_pcm_to_mel(State & st, const float * samples, int n_samples) {
+bool stage_pcm_to_mel(State & st, const float * samples, int n_samples, bool sync) {
     Context & ctx = *st.ctx;
     const int64_t t0 = time_us();
     WB_CUDA_OK(cudaSetDevice(ctx.model.device));
@@ -389,11 +394,22 @@ bool stage_pcm_to_mel(State & st, const float * samples, int n_samples) {
     WB_CUDA_OK(cudaMemcpyAsync(st.d_pcm, samples, (size_t) n_samples * sizeof(float), cudaMemcpyDefault /* host or device PCM */, ctx.stream));
     MelTables tab{ctx.model.mel_sin, ctx.model.mel_cos, ctx.model.mel_hann, ctx.model.mel_filters_t, n_mel};
     if (!mel_compute(tab, st.d_pcm, n_samples, n_len, st.d_mel, st.d_melmax, ctx.stream)) return false;
-    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    // sync == false: the caller batches the front end of many states and synchronises once (stage_mel_sync); nothing on the host
+    // depends on the result, and the encoder consumes it on the same stream
+    if (sync) WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
     st.n_mel = n_mel;
     st.n_len = n_len;
     st.n_len_org = mel_n_len_org(n_samples);
     st.t_mel_us += time_us() - t0;
+    return true;
+}
+
+// one synchronisation for a batch of stage_pcm_to_mel(..., sync = false); the wait is shared out to the states' mel timers
+bool stage_mel_sync(Context & ctx, State * const * states, int n) {
+    const int64_t t0 = time_us();
+    WB_CUDA_OK(cudaStreamSynchronize(ctx.stream));
+    const int64_t dt = time_us() - t0;
+    for (int i = 0; i < n; ++i) states[i]->t_mel_us += dt / std::max(1, n);
     return true;
 }
 
@@ -624,6 +640,12 @@ bool stage_encode(Context & ctx, State * const * states, const int * mel_offsets
 bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
     WB_CUDA_OK(cudaSetDevice(ctx.model.device));
     const int64_t t0 = time_us();
+    static const bool dlog = getenv("WB200_DECODE_LOG") != nullptr;  // debugging aid: host-clock phases of the general path (adds syncs)
+    auto mark = [&](const char * what) {
+        if (!dlog) return;
+        cudaStreamSynchronize(ctx.stream);
+        fprintf(stderr, "stage_decode n=%d %s +%lld us\n", n, what, (long long) (time_us() - t0));
+    };
     const Model & m = ctx.model;
     const auto & hp = m.hp;
     const int S = hp.n_text_state, H = hp.n_text_head, L = hp.n_text_layer, V = hp.n_vocab;
@@ -649,8 +671,10 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
         i += cnt;
     }
     for (int i = 0; i < n; ++i) n_flag += rows[i].want_logits ? 1 : 0;
+    mark("slots");
     if (!ensure_dec_ws(ctx, std::max(n, 8), std::max(n_flag, MAX_DECODERS), max_cells)) return false;
     DecWorkspace & ws = ctx.dec_ws;
+    mark("workspace");
 
     // staging layout: tokens | pos | SelfKvRow[] | CrossKvRow[] | cell lists
     uint8_t * hs = ws.h_stage;
@@ -726,6 +750,7 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
     const int T = rows[0].st->cross_T;
     for (int i = 1; i < n; ++i) WB_CHECK(rows[i].st->cross_T == T, "mixed audio contexts in one decode batch\n");
 
+    mark("staged");
     g_prof_gemm_cat = PC_GEMM_DEC;
     if (!embed_tokens(m.d_te, m.d_pe, d_tok, d_pos, n, S, ws.x, s)) return false;
     const float kq_scale = (float) pow((double) 64.0f, -0.25);  // wc:2522
@@ -767,6 +792,7 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
             if (!gemm_f16_tc(opnd(ws.hb, n, 4 * S), opnd(l.fc2.w, S, 4 * S), n, S, 4 * S, 1, e2, 0, s)) return false;
         }
     }
+    mark("layers");
     // final norm + tied-embedding logits, only for the rows whose logits are requested (wc:2821-2835, 2965-2971)
     if (n_flag > 0) {
         if (!layernorm_rows(ws.x, n, S, m.d_ln.g, m.d_ln.b, hp.eps, ws.xa, nullptr, s)) return false;
@@ -785,6 +811,7 @@ bool stage_decode(Context & ctx, const BatchRow * rows, int n, bool save_qk) {
         GemmEpilogue e = epi_row(ws.logits, false, V);
         if (!gemm_f16_tc(opnd(a_rows, n_flag, S), opnd(m.d_te, V, S), n_flag, V, S, 1, e, 0, s)) return false;
     }
+    mark("logits");
     // timing buckets of the reference (wc:2982-2991) per state
     int n_states = 0;
     for (int i = 0; i < n; ++i) n_states += (i == 0 || rows[i].st != rows[i - 1].st) ? 1 : 0;

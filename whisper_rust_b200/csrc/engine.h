@@ -191,7 +191,8 @@ State * state_create(Context * ctx);
 bool kv_self_alloc(State & st, int n_ctx);
 
 // --- stages.  All return false on failure (logged).
-bool stage_pcm_to_mel(State & st, const float * samples, int n_samples);
+bool stage_pcm_to_mel(State & st, const float * samples, int n_samples, bool sync = true);
+bool stage_mel_sync(Context & ctx, State * const * states, int n);
 bool stage_set_mel(State & st, const float * data, int n_len, int n_mel);
 bool stage_get_mel(State & st, std::vector<float> & out);
 // Encodes one window of each listed state (mel offsets per state) as one batch, then fills their cross caches.

@@ -1141,6 +1141,18 @@ int lang_auto_detect(Context * ctx, State * st, int offset_ms, float * lang_prob
 // token), admits newly submitted jobs — and later windows of running ones — at step boundaries into the decode lanes, and
 // wakes each caller when its job is done.  whisper_b200_full_batch and whisper_full_parallel are clients of the same queue.
 // User callbacks are handed back to the thread that made the call and run there while the worker waits.
+// WB200_SCHED_LOG=<file>: one line per scheduler event (microseconds since the first event): where the wall time of a call goes
+static void sched_log(const char * what, long a = 0, long b = 0) {
+    static FILE * f = [] {
+        const char * p = getenv("WB200_SCHED_LOG");
+        return p ? fopen(p, "a") : (FILE *) nullptr;
+    }();
+    if (!f) return;
+    static const int64_t t0 = time_us();
+    fprintf(f, "%lld %s %ld %ld\n", (long long) (time_us() - t0), what, a, b);
+    fflush(f);
+}
+
 struct Client {
     std::condition_variable cv;
     const std::function<void()> * pending_fn = nullptr;  // a callback the worker wants run on the owner's thread
@@ -1162,6 +1174,7 @@ struct Lane {
     std::vector<Decoder *> sdecs;
     std::vector<FullJob *> sjobs;  // the job behind every sampler row
     bool pending = false;          // a fused step is in flight on this lane's stream
+    int last_logged_rows = -1;     // WB200_SCHED_LOG: row count of the last logged fused step
     int n_lanes_at_launch = 1;
 };
 
@@ -1363,6 +1376,7 @@ void Scheduler::encode_jobs(Lane & ln, const std::vector<FullJob *> & cand) {
         }
     }
     if (ln.enc_jobs.empty()) return;
+    sched_log("encode_begin", (long) ln.enc_jobs.size(), n_live);
     if (!stage_encode(*ctx, ln.enc_states.data(), ln.enc_offsets.data(), (int) ln.enc_jobs.size())) {
         log_error("%s: failed to encode\n", __func__);
         for (auto * j : ln.enc_jobs) j->finish(-6);
@@ -1375,18 +1389,31 @@ void Scheduler::encode_jobs(Lane & ln, const std::vector<FullJob *> & cand) {
 // mel, call set-up (wc:6801-6984), lane assignment and the first encoder pass of newly submitted jobs
 void Scheduler::admit(std::vector<FullJob *> & incoming) {
     std::vector<FullJob *> fresh;
+    // the log-mel front end of every arrival is launched back to back and waited for ONCE (per-state synchronisation made the
+    // front end launch-bound: 0.19 ms per 30 s window for 3.5 MB of traffic)
+    std::vector<State *> mel_states;
     for (FullJob * j : incoming) {
         j->admitted = true;
         j->st->result_all.clear();
         j->mask = suppress_mask(*ctx, j->params);
         if (!j->mask) {
             j->finish(-6);
-        } else if (j->n_samples > 0 && !stage_pcm_to_mel(*j->st, j->samples, j->n_samples)) {  // wc:6806-6812
-            log_error("%s: failed to compute log mel spectrogram\n", "whisper_full_with_state");
-            j->finish(-2);
-        } else {
-            j->init();
+        } else if (j->n_samples > 0) {
+            if (!stage_pcm_to_mel(*j->st, j->samples, j->n_samples, false)) {  // wc:6806-6812
+                log_error("%s: failed to compute log mel spectrogram\n", "whisper_full_with_state");
+                j->finish(-2);
+            } else {
+                mel_states.push_back(j->st);
+            }
         }
+    }
+    sched_log("admit_begin", (long) incoming.size(), n_live);
+    if (!mel_states.empty() && !stage_mel_sync(*ctx, mel_states.data(), (int) mel_states.size())) {
+        for (FullJob * j : incoming)
+            if (j->phase != FullJob::DONE) j->finish(-2);
+    }
+    for (FullJob * j : incoming) {
+        if (j->phase != FullJob::DONE) j->init();
         if (j->phase == FullJob::DONE) job_done(j);
         else fresh.push_back(j);
     }
@@ -1407,8 +1434,10 @@ void Scheduler::admit(std::vector<FullJob *> & incoming) {
         lanes[(size_t) best].jobs.push_back(fresh[k]);
     }
     n_live += (int) fresh.size();
+    sched_log("mel_done", (long) fresh.size(), n_live);
     Lane scratch;
     encode_jobs(scratch, fresh);  // the first windows of every lane go through the encoder as one batch
+    sched_log("admit_encode_done", (long) fresh.size(), n_live);
 }
 
 void Scheduler::reap() {
@@ -1425,6 +1454,7 @@ void Scheduler::reap() {
             ln.sdecs.clear();
         }
         n_live -= (int) done.size();
+        sched_log("jobs_done", (long) done.size(), n_live);
         for (FullJob * j : done) job_done(j);  // the job's memory belongs to its caller from here on
     }
 }
@@ -1539,6 +1569,10 @@ void Scheduler::lane_advance(int lane_id) {
         const bool fused_step = !any_callback && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
         bool ok;
         if (fused_step) {
+            if (n_rows != ln.last_logged_rows) {
+                sched_log("lane_step_rows", lane_id, n_rows);
+                ln.last_logged_rows = n_rows;
+            }
             // one token per sequence: the whole decoder forward + sampler is one CUDA-graph launch (step.cu)
             ok = stage_step_launch(*ctx, lane_id, active_lanes(), ln.rows.data(), n_rows, sst, ln.srows.data());
             if (ok) {
@@ -1546,8 +1580,11 @@ void Scheduler::lane_advance(int lane_id) {
                 return;
             }
         } else {
+            sched_log("general_decode_begin", lane_id, n_rows);
             ok = stage_decode(*ctx, ln.rows.data(), n_rows, false) &&
                  stage_sample(*ctx, sst, ln.srows.data(), (int) ln.srows.size(), any_dists, ln.sdecs.data(), any_callback ? &prefilter : nullptr);
+            sched_log("general_decode_end", lane_id, n_rows);
+            ln.last_logged_rows = -1;
         }
         if (!ok) {
             log_error("%s: failed to decode\n", __func__);
