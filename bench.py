@@ -54,8 +54,12 @@ def model_path(arch: str) -> Path:
 def workload_config(args, world):
     """`config` of both arms: the workload BASELINE.json's metric is quoted on, as it runs here."""
     B = args.batch
+    via = {"batch": "whisper_b200_full_batch",
+           "threads": f"whisper_full_with_state from {B} host threads (one WhisperState each), joined after every step",
+           "stream": f"whisper_full_with_state from {B} host threads (one WhisperState each) draining the queue of all steps' shards, no "
+                     f"barrier between steps"}[getattr(args, "api", "batch")]
     return {"workload": f"whisper {args.model} (random-init ggml layout, seed {RECIPE.seed}, te_std {RECIPE.te_std}) greedy best_of=1 "
-                        f"temperature_inc=0, {B} x {args.seconds:.0f} s synthetic shards per GPU per step via whisper_b200_full_batch; "
+                        f"temperature_inc=0, {B} x {args.seconds:.0f} s synthetic shards per GPU per step via {via}; "
                         f"working set (weights + KV) >> L2, no flush needed",
             "checkpoint_arch": args.model, "batch_per_gpu": B, "parallelism": f"shard-by-window x{world}"}
 
@@ -307,11 +311,14 @@ def main():
 
     lib.whisper_b200_full_stream.restype = C.c_int
     lib.whisper_b200_full_stream.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, api.whisper_full_params, C.POINTER(C.POINTER(C.c_float)),
-                                             C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+                                             C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_int)]
+
+    last_item = (C.c_int * B)(*([-1] * B))   # stream mode: which queue entry (step * B + shard) every state transcribed last
 
     def stream(sets, rounds, read_back):
-        """`stream`: B host threads, thread i transcribes shard i of step 0, 1, ... back to back through the unchanged
-        whisper_full_with_state (a server's worker threads draining their queues); no barrier between the steps"""
+        """`stream`: B worker threads (one state each) drain the queue of the rounds * B shards of all steps through the unchanged
+        whisper_full_with_state, each taking the next shard when its previous call returns (a server's thread pool); no barrier
+        between the steps"""
         pp = (C.POINTER(C.c_float) * (B * rounds))()
         for r in range(rounds):
             t = sets[r % n_sets]
@@ -319,7 +326,7 @@ def main():
                 pp[r * B + i] = C.cast(t[i].data_ptr(), C.POINTER(C.c_float))
         nb = C.c_uint64(0)
         rc = lib.whisper_b200_full_stream(ctx.ptr, st_arr, B, p.fp, pp, (C.c_int * (B * rounds))(*([n_samples] * (B * rounds))), rounds,
-                                          1 if read_back else 0, C.byref(nb))
+                                          1 if read_back else 0, C.byref(nb), last_item)
         if rc != 0:
             raise SystemExit(f"whisper_b200_full_stream failed: {rc}")
         return int(nb.value)
@@ -377,6 +384,17 @@ def main():
         ms_e2e, d2h = ms_dev, 0
     else:
         ms_e2e, _, d2h = timed(host_sets, True)
+
+    # CPU baseline + parity NOW, while the states still hold the results of the last timed (e2e) pass
+    cpu_par = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and cf.ORACLE_LIB.exists():
+        def clip_of_state(i):
+            """the host PCM state i transcribed LAST in the timed e2e pass (stream: whichever queue entry its thread took last)"""
+            if args.api == "stream":
+                k = last_item[i]
+                return host_sets[(k // B) % n_sets][k % B].numpy()
+            return host_sets[(args.steps - 1) % n_sets][i].numpy()
+        cpu_par = cpu_baseline(args, cf, ctx, lib, states, clip_of_state)
 
     # the other entry point on the same workload (one warm-up + the timed steps, PCM resident): the cost of being a true drop-in
     other = "batch" if args.api in ("threads", "stream") else "threads"
@@ -493,8 +511,8 @@ def main():
             "decode_ms_per_30s_window": round(max(0.0, ms_dev / args.steps - phase["encode"] - phase["mel"]) / B, 4),
             "kernel_breakdown_ms_per_step_est": {k: round(x / args.steps, 3) for k, x in sorted(est.items(), key=lambda kv: -kv[1])},
         }
-        if world == 1 and not args.no_cpu_baseline and cf.ORACLE_LIB.exists():
-            out["cpu_baseline"], out["parity"] = cpu_baseline(args, cf, ctx, lib, states, host_sets[(args.steps - 1) % n_sets])
+        if cpu_par is not None:
+            out["cpu_baseline"], out["parity"] = cpu_par
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -604,7 +622,7 @@ def run_clip(args, lib, ctx, rank, world, local_rank, torch, dist, barrier):
         s_.free()
 
 
-def cpu_baseline(args, cf, ctx_gpu, lib_gpu, states, host_set):
+def cpu_baseline(args, cf, ctx_gpu, lib_gpu, states, clip_of_state):
     """The reference CPU engine (-march=native build) on a bounded sample of the same workload: N_PARITY shards of the last timed
     step, spread over every decode lane, one thread per physical core.  Each shard's transcript is diffed token by token (ids and
     segment times) against what the CUDA path produced for that shard inside the timed region; one multi-window clip (47.3 s: partial
@@ -627,7 +645,7 @@ def cpu_baseline(args, cf, ctx_gpu, lib_gpu, states, host_set):
     p = make_params(ref, cores)
     shards, t_total = [], 0.0
     for i in picks:
-        clip = host_set[i].numpy()
+        clip = clip_of_state(i)
         t0 = time.perf_counter()
         st.full(p, clip)
         dt = time.perf_counter() - t0
@@ -637,10 +655,41 @@ def cpu_baseline(args, cf, ctx_gpu, lib_gpu, states, host_set):
         shards.append({"shard": i, "identical": a == b, "n_tokens_ref": len(ia), "n_tokens_b200": len(ib),
                        "n_equal_prefix": next((k for k, (x, y) in enumerate(zip(ia, ib)) if x != y), min(len(ia), len(ib))),
                        "cpu_s": round(dt, 2)})
+    # A shard that differs: is it a near-tie?  Re-run the reference on it with a logits_filter_callback (wc:6226-6228) that records the
+    # top-1 / top-2 logit gap of every step, and ask the reference's OTHER build (AVX2) which side it takes at the first differing token.
+    for rec in [x for x in shards if not x["identical"]][:2]:
+        clip = clip_of_state(rec["shard"])
+        k = rec["n_equal_prefix"]
+        steps_seen = []
+        V = ctx.n_vocab()
+
+        def on_logits(_c, _s, _tok, _n, logits, _ud):
+            a = np.ctypeslib.as_array(logits, shape=(V,))
+            top = np.argpartition(a, -2)[-2:]
+            top = top[np.argsort(a[top])]
+            steps_seen.append((int(top[1]), int(top[0]), float(a[top[1]] - a[top[0]])))
+        pq = make_params(ref, cores)
+        pq.set_logits_filter_callback(on_logits)
+        st.full(pq, clip)
+        ids_b = [t for sg in seg_key(states[rec["shard"]]) for t in sg[2]]
+        if k < len(steps_seen) and k < len(ids_b):
+            t1, t2, gap = steps_seen[k]
+            rec["first_difference"] = {"token_index": k, "reference_top1": t1, "reference_top2": t2, "reference_top1_minus_top2_logit": gap,
+                                       "b200_token": ids_b[k], "b200_token_is_reference_top2": ids_b[k] == t2}
+        if cf.ORACLE_LIB.exists() and path != cf.ORACLE_LIB:
+            alt = api.load_library(cf.ORACLE_LIB)
+            api.install_quiet_logging(alt)
+            c2 = WhisperContext.new_with_params(model_path(args.model), WhisperContextParameters(use_gpu=False), lib=alt)
+            s2 = c2.create_state()
+            s2.full(make_params(alt, cores), clip)
+            ids_alt = [t for sg in seg_key(s2) for t in sg[2]]
+            rec["reference_avx2_build_token_at_difference"] = ids_alt[k] if k < len(ids_alt) else None
+            rec["reference_avx2_build_identical_to_b200"] = ids_alt == ids_b
+            s2.free(); c2.free()
     # the reference's default thread count, one shard
     p4 = make_params(ref, min(4, logical))
     t0 = time.perf_counter()
-    st.full(p4, host_set[picks[0]].numpy())
+    st.full(p4, clip_of_state(picks[0]))
     dt4 = time.perf_counter() - t0
     # one multi-window clip through both engines (the GPU side through the plain whisper_full_with_state)
     clip_mw = synth.synth_audio(47.3, seed=4242)
@@ -656,7 +705,13 @@ def cpu_baseline(args, cf, ctx_gpu, lib_gpu, states, host_set):
             "sample": f"{len(picks)} x {args.seconds:.0f} s shards of the same workload (shards {picks}), n_threads={cores} (physical cores), "
                       f"{t_total:.1f} s wall, {build}",
             "at_reference_default_threads": {"n_threads": min(4, logical), "value": args.seconds / dt4, "sample": "1 shard"}}
+    near_tie = [x for x in shards if not x["identical"] and (x.get("reference_avx2_build_identical_to_b200") or
+                (x.get("first_difference", {}).get("b200_token_is_reference_top2") and
+                 abs(x["first_difference"]["reference_top1_minus_top2_logit"]) < 5e-3))]
     par = {"token_ids_identical": bool(all(x["identical"] for x in shards) and multi["identical"]),
+           "differing_shards_explained_as_reference_near_ties": len(near_tie),
+           "note": "a differing shard counts as a near-tie when the reference's own AVX2 build gives the b200 transcript, or the b200 token is the "
+                   "reference's runner-up within 5e-3 in logit at the first differing step (its two builds disagree at that size: DESIGN.md 2)",
            "shards_identical": sum(1 for x in shards if x["identical"]), "shards_compared": len(shards), "shards": shards,
            "multi_window_clip": multi, "compared": "segment t0/t1 and token ids, reference CPU engine vs the CUDA path's output of the timed region"}
     st.free(); ctx.free()

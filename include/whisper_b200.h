@@ -28,12 +28,13 @@ WHISPER_API int whisper_b200_full_batch(struct whisper_context * ctx, struct whi
 WHISPER_API int whisper_b200_full_threads(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
                                           struct whisper_full_params params, const float * const * samples, const int * n_samples);
 
-/* The same harness as a stream: thread i transcribes samples[r * n_states + i], r = 0 .. rounds-1, back to back on states[i] (no barrier
- * between rounds; the scheduler admits a thread's next clip while other clips are still decoding).  read_back != 0: every call's result is
- * read through the public accessors; *bytes_read (optional) receives the bytes read. */
+/* The same harness as a stream: n_states worker threads (one state each) drain a shared queue of rounds * n_states clips, samples[k] /
+ * n_samples[k]; a thread takes the next clip as soon as its previous whisper_full_with_state call returns (no barrier between rounds; the
+ * scheduler admits it while other clips are still decoding).  read_back != 0: every call's result is read through the public accessors;
+ * *bytes_read (optional) receives the bytes read; last_item[i] (optional) the queue index of the last clip states[i] transcribed. */
 WHISPER_API int whisper_b200_full_stream(struct whisper_context * ctx, struct whisper_state ** states, int n_states,
                                          struct whisper_full_params params, const float * const * samples, const int * n_samples,
-                                         int rounds, int read_back, uint64_t * bytes_read);
+                                         int rounds, int read_back, uint64_t * bytes_read, int * last_item);
 
 /* Batched stage entry points (same contracts as whisper_encode_with_state / whisper_decode_with_state, wc:3933-3971). */
 WHISPER_API int whisper_b200_encode_batch(struct whisper_context * ctx, struct whisper_state ** states, const int * offsets, int n_states);

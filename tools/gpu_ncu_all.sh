@@ -1,9 +1,9 @@
 #!/bin/bash
 # ncu --set full of every kernel the hot path names, one capture per kernel from the SHIPPING build at the bench's per-lane shapes
-# (large-v3, one lane of 96 sequences), plus the DTW kernels from the alignment test.  Summaries -> $OUT/<name>.txt
+# (large-v3, one lane of 112 sequences = a lane of the default 448-shard bench step), plus the DTW kernels from the alignment test.  Summaries -> $OUT/<name>.txt
 set -u
 OUT=gpurun_out/${1:-ncu_all}; mkdir -p $OUT
-BCMD="python bench.py --batch 96 --steps 1 --warmup 1 --no-extras --no-cpu-baseline --api batch"
+BCMD="python bench.py --batch 112 --steps 1 --warmup 1 --no-extras --no-cpu-baseline --api batch"
 DCMD="python -m pytest tests/test_dtw.py -q -x -k alignment_chain"
 cap() { # name regex skip count cmd...
   name=$1; rx=$2; skip=$3; cnt=$4; shift 4

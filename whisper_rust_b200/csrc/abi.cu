@@ -4,6 +4,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <regex>
 #include <thread>
 
@@ -574,25 +575,37 @@ int whisper_b200_full_threads(struct whisper_context * ctx, struct whisper_state
     WB_CATCH(-1)
 }
 
-// The same harness as a stream of work: thread i transcribes samples[r * n_states + i] for r = 0 .. rounds-1 back to back on its own
-// state (a worker thread of a server draining its queue).  There is no barrier between rounds: a thread submits its next clip as soon
-// as its previous call returns, and the scheduler admits it while other threads' clips are still decoding.  With read_back != 0 every
-// call's result is read through the public accessors (segments, times, text, token data) like a caller would; *bytes_read sums them.
+// The same harness as a stream of work: n_states worker threads (one WhisperState each) drain a shared queue of rounds * n_states clips,
+// samples[0 .. rounds * n_states), each thread taking the next clip as soon as its previous whisper_full_with_state call returns (a
+// server's thread pool).  There is no barrier between rounds: the scheduler admits a thread's next clip while other clips are still
+// decoding.  With read_back != 0 every call's result is read through the public accessors (segments, times, text, token data) like a
+// caller would; *bytes_read sums them.  last_item[i] (optional) receives the queue index of the last clip state i transcribed.
 int whisper_b200_full_stream(struct whisper_context * ctx, struct whisper_state ** states, int n_states, struct whisper_full_params params,
-                             const float * const * samples, const int * n_samples, int rounds, int read_back, uint64_t * bytes_read) {
+                             const float * const * samples, const int * n_samples, int rounds, int read_back, uint64_t * bytes_read,
+                             int * last_item) {
     WB_TRY
     if (!ctx || !states || n_states <= 0 || !samples || !n_samples || rounds <= 0) return -1;
-    std::vector<int> rc((size_t) n_states, 0);
+    const int n_items = rounds * n_states;
+    std::atomic<int> next{0};
+    std::atomic<int> first_error{0};
     std::vector<uint64_t> nb((size_t) n_states, 0);
     std::vector<std::thread> th;
     th.reserve((size_t) n_states);
     for (int i = 0; i < n_states; ++i)
         th.emplace_back([&, i] {
             whisper_state * st = states[i];
-            for (int r = 0; r < rounds && rc[(size_t) i] == 0; ++r) {
-                const size_t k = (size_t) r * n_states + i;
-                rc[(size_t) i] = whisper_full_with_state(ctx, st, params, samples[k], n_samples[k]);
-                if (!read_back || rc[(size_t) i] != 0) continue;
+            if (last_item) last_item[i] = -1;
+            while (first_error.load() == 0) {
+                const int k = next.fetch_add(1);
+                if (k >= n_items) break;
+                const int rc = whisper_full_with_state(ctx, st, params, samples[k], n_samples[k]);
+                if (rc != 0) {
+                    int zero = 0;
+                    first_error.compare_exchange_strong(zero, rc);
+                    break;
+                }
+                if (last_item) last_item[i] = k;
+                if (!read_back) continue;
                 const int ns = whisper_full_n_segments_from_state(st);
                 for (int sgi = 0; sgi < ns; ++sgi) {
                     const char * txt = whisper_full_get_segment_text_from_state(st, sgi);
@@ -612,9 +625,7 @@ int whisper_b200_full_stream(struct whisper_context * ctx, struct whisper_state 
         *bytes_read = 0;
         for (uint64_t b : nb) *bytes_read += b;
     }
-    for (int r : rc)
-        if (r != 0) return r;
-    return 0;
+    return first_error.load();
     WB_CATCH(-1)
 }
 
