@@ -481,6 +481,10 @@ def main():
                 ent = tr.get(roofline["kernel"], {})
                 if ent.get("batch_per_gpu") == B and ent.get("model") == args.model:
                     roofline["traffic"] = ent["dram_bytes_per_launch"]
+                    # the ncu capture is ONE full lane (rows_per_launch); `algorithmic_bytes_per_launch` above averages over the sampled
+                    # launches incl. the short straggler lanes, so compare `traffic` with the figure below, not with that average
+                    roofline["traffic_algorithmic_bytes_same_launch"] = ent.get("algorithmic_bytes_per_launch")
+                    roofline["traffic_rows_per_launch"] = ent.get("rows_per_launch")
                     roofline["traffic_source"] = ent.get("source")
             except Exception:
                 pass
@@ -534,12 +538,14 @@ def run_clip(args, lib, ctx, rank, world, local_rank, torch, dist, barrier):
     clip_host = None
     if rank == 0:   # the clip: n_shards distinct 30 s pieces, contiguous in pinned host memory
         clip_host = torch.from_numpy(np.stack([synth.synth_audio(args.seconds, seed=7000 + i) for i in range(n_shards)])).pin_memory()
-    n_states = min(args.batch, max(1, len(mine)))
+    # equal-size batches: 960 shards on one GPU run as 3 x 320, not 448 + 448 + 64
+    n_batches = max(1, -(-len(mine) // args.batch))
+    n_states = max(1, -(-len(mine) // n_batches))
     states = [ctx.create_state() for _ in range(n_states)]
     p = make_params(lib)
     lib.whisper_b200_full_threads.restype = C.c_int
     lib.whisper_b200_full_threads.argtypes = lib.whisper_b200_full_batch.argtypes
-    fn = lib.whisper_b200_full_threads if args.api == "threads" else lib.whisper_b200_full_batch
+    fn = lib.whisper_b200_full_batch if args.api == "batch" else lib.whisper_b200_full_threads   # stream == threads: one batch per pass
     recv = torch.empty((n_max, n_samples), dtype=torch.float32, device=dev)
 
     def one_pass():
