@@ -120,3 +120,17 @@ def test_no_device_means_loud_failure_not_a_cpu_path():
             assert any(b"no CUDA device" in m or b"CPU path" in m for _, m in logs), logs[-3:]
     finally:
         api.install_quiet_logging(lib)
+
+
+def test_use_gpu_false_is_refused_with_a_log_line():
+    """there is no CPU path: a context asked for with use_gpu = false is not silently run on the GPU"""
+    lib = api.load_library()
+    logs = []
+    cb = api.LOG_CB(lambda lvl, msg, ud: logs.append((lvl, msg)))
+    lib.whisper_log_set(C.cast(cb, C.c_void_p), None)
+    try:
+        with pytest.raises(api.WhisperError):
+            WhisperContext.new_from_buffer_with_params(synth.model_bytes("micro", with_tensors=False), WhisperContextParameters(use_gpu=False), lib=lib)
+        assert any(b"use_gpu = false" in m for _, m in logs), logs[-3:]
+    finally:
+        api.install_quiet_logging(lib)
