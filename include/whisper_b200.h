@@ -45,6 +45,9 @@ WHISPER_API int whisper_b200_decode_batch(struct whisper_context * ctx, struct w
 /* Probes: copy a stage output to host memory.  Return the element count (or -1); copy only when cap is large enough. */
 WHISPER_API int64_t whisper_b200_get_mel(struct whisper_state * state, float * dst, int64_t cap, int * n_len, int * n_len_org, int * n_mel);
 WHISPER_API int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int window, float * dst, int64_t cap);   /* [n_ctx][n_state] */
+/* VAD host-logic test hook: replace the probabilities of a VAD context (so that whisper_vad_segments_from_probs can be checked against
+ * the reference on arbitrary sequences, also without a device) */
+WHISPER_API int whisper_b200_test_vad_set_probs(struct whisper_vad_context * vctx, const float * probs, int n);
 /* E1 alone (wc:1994-2054): conv stem of the window at mel_offset, without the positional embedding = whisper_state::embd_conv; f32 [T][S] */
 WHISPER_API int64_t whisper_b200_test_conv_stem(struct whisper_context * ctx, struct whisper_state * state, int mel_offset, float * dst, int64_t cap);
 WHISPER_API int64_t whisper_b200_get_kv_cross(struct whisper_state * state, uint16_t * dst, int64_t cap);            /* f16 [L][2H][T][64] */

@@ -13,6 +13,7 @@
 #include "step.cuh"
 #include "log.h"
 #include "prof.h"
+#include "vad.h"
 
 using namespace wb;
 
@@ -519,10 +520,8 @@ static int unsupported_params(const whisper_full_params & params, const char * f
         log_error("%s: grammar-constrained sampling (grammar_rules) is not implemented by this library\n", fn);
         return -10;
     }
-    if (params.vad) {
-        log_error("%s: params.vad = true, but the Silero VAD front end is not implemented by this library\n", fn);
-        return -11;
-    }
+    // params.vad is read by whisper_full / whisper_full_parallel only, exactly as in the reference (wc:7720, 7748): whisper_full_with_state
+    // itself never looks at it (wc:6795-7711), so a vad = true arriving here transcribes the samples it is given
     return 0;
 }
 
@@ -535,9 +534,35 @@ int whisper_full_with_state(struct whisper_context * ctx, struct whisper_state *
     return full_with_states(ctx, &sp, 1, &params, false, &samples, &n_samples);
     WB_CATCH(-1)
 }
+// the VAD step shared by whisper_full and whisper_full_parallel (wc:7718-7733, 7746-7761): 1 = continue with the filtered samples,
+// 0 = no speech (empty result, return 0), -1 = failure.  The PCM must be host memory on this path (the filter is a host-side gather).
+static int vad_step(struct whisper_context * ctx, const whisper_full_params & params, const float *& samples, int & n_samples, std::vector<float> & keep,
+                    bool clear_on_silence) {
+    if (!params.vad) return 1;
+    log_msg(GGML_LOG_LEVEL_INFO, "%s: VAD is enabled, processing speech segments only\n", __func__);
+    bool ok = false;
+    const bool ran = sched_run(ctx, [&] { ok = vad_filter(ctx, ctx->state, params, samples, n_samples, keep); });
+    if (!ran || !ok) {
+        log_error("%s: failed to compute VAD\n", __func__);
+        return -1;
+    }
+    if (keep.empty()) {
+        if (clear_on_silence) ctx->state->result_all.clear();   // whisper_full clears (wc:7727), whisper_full_parallel does not (wc:7753)
+        return 0;
+    }
+    samples = keep.data();
+    n_samples = (int) keep.size();
+    return 1;
+}
+
 int whisper_full(struct whisper_context * ctx, struct whisper_full_params params, const float * samples, int n_samples) {
+    WB_TRY
     if (!ctx || !ctx->state) return -1;
+    std::vector<float> vad_samples;
+    const int v = vad_step(ctx, params, samples, n_samples, vad_samples, true);
+    if (v <= 0) return v;
     return whisper_full_with_state(ctx, static_cast<whisper_state *>(ctx->state), params, samples, n_samples);
+    WB_CATCH(-1)
 }
 
 int whisper_b200_full_batch(struct whisper_context * ctx, struct whisper_state ** states, int n_states, struct whisper_full_params params,
@@ -635,6 +660,11 @@ int whisper_full_parallel(struct whisper_context * ctx, struct whisper_full_para
     WB_TRY
     if (!ctx || !ctx->state) return -1;
     if (n_processors <= 1) return whisper_full(ctx, params, samples, n_samples);
+    std::vector<float> vad_samples;
+    {
+        const int v = vad_step(ctx, params, samples, n_samples, vad_samples, false);
+        if (v <= 0) return v;
+    }
     const int offset_samples = (WHISPER_SAMPLE_RATE * params.offset_ms) / 1000;
     const int n_per = (n_samples - offset_samples) / n_processors;
     std::vector<whisper_state *> extra;
@@ -699,10 +729,22 @@ int whisper_full_n_segments_from_state(struct whisper_state * state) { return (i
 int whisper_full_n_segments(struct whisper_context * ctx) { return (int) ctx->state->result_all.size(); }
 int whisper_full_lang_id_from_state(struct whisper_state * state) { return state->lang_id; }
 int whisper_full_lang_id(struct whisper_context * ctx) { return ctx->state->lang_id; }
-int64_t whisper_full_get_segment_t0_from_state(struct whisper_state * state, int i) { return SEG(state, i).t0; }
-int64_t whisper_full_get_segment_t0(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).t0; }
-int64_t whisper_full_get_segment_t1_from_state(struct whisper_state * state, int i) { return SEG(state, i).t1; }
-int64_t whisper_full_get_segment_t1(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).t1; }
+// segment times: mapped back to the caller's audio when the state's last whisper_full ran on VAD-filtered samples (wc:7927-7960)
+int64_t whisper_full_get_segment_t0_from_state(struct whisper_state * state, int i) {
+    const int64_t t0 = SEG(state, i).t0;
+    if (!state->has_vad_segments || state->vad_mapping.empty()) return t0;
+    return vad_map_time(*state, t0);
+}
+int64_t whisper_full_get_segment_t1_from_state(struct whisper_state * state, int i) {
+    const int64_t t1 = SEG(state, i).t1;
+    if (!state->has_vad_segments || state->vad_mapping.empty()) return t1;
+    int64_t o1 = vad_map_time(*state, t1);
+    const int64_t o0 = whisper_full_get_segment_t0_from_state(state, i);
+    if (o1 - o0 < 10) o1 = o0 + 10;   // no zero-length segments
+    return o1;
+}
+int64_t whisper_full_get_segment_t0(struct whisper_context * ctx, int i) { return whisper_full_get_segment_t0_from_state(static_cast<whisper_state *>(ctx->state), i); }
+int64_t whisper_full_get_segment_t1(struct whisper_context * ctx, int i) { return whisper_full_get_segment_t1_from_state(static_cast<whisper_state *>(ctx->state), i); }
 bool whisper_full_get_segment_speaker_turn_next_from_state(struct whisper_state * state, int i) { return SEG(state, i).speaker_turn_next; }
 bool whisper_full_get_segment_speaker_turn_next(struct whisper_context * ctx, int i) { return SEG(ctx->state, i).speaker_turn_next; }
 const char * whisper_full_get_segment_text_from_state(struct whisper_state * state, int i) { return SEG(state, i).text.c_str(); }
@@ -735,19 +777,7 @@ struct whisper_vad_context_params whisper_vad_default_context_params(void) {
     r.gpu_device = 0;
     return r;
 }
-static void vad_unavailable(const char * fn) { log_error("%s: the Silero VAD front end is not part of this library\n", fn); }
-struct whisper_vad_context * whisper_vad_init_from_file_with_params(const char *, struct whisper_vad_context_params) { vad_unavailable(__func__); return nullptr; }
-struct whisper_vad_context * whisper_vad_init_with_params(struct whisper_model_loader *, struct whisper_vad_context_params) { vad_unavailable(__func__); return nullptr; }
-bool whisper_vad_detect_speech(struct whisper_vad_context *, const float *, int) { vad_unavailable(__func__); return false; }
-int whisper_vad_n_probs(struct whisper_vad_context *) { return 0; }
-float * whisper_vad_probs(struct whisper_vad_context *) { return nullptr; }
-struct whisper_vad_segments * whisper_vad_segments_from_probs(struct whisper_vad_context *, struct whisper_vad_params) { vad_unavailable(__func__); return nullptr; }
-struct whisper_vad_segments * whisper_vad_segments_from_samples(struct whisper_vad_context *, struct whisper_vad_params, const float *, int) { vad_unavailable(__func__); return nullptr; }
-int whisper_vad_segments_n_segments(struct whisper_vad_segments *) { return 0; }
-float whisper_vad_segments_get_segment_t0(struct whisper_vad_segments *, int) { return 0.0f; }
-float whisper_vad_segments_get_segment_t1(struct whisper_vad_segments *, int) { return 0.0f; }
-void whisper_vad_free_segments(struct whisper_vad_segments *) {}
-void whisper_vad_free(struct whisper_vad_context *) {}
+// whisper_vad_* : vad_api.cu
 int whisper_bench_memcpy(int) { return 0; }
 const char * whisper_bench_memcpy_str(int) { return "not available: use bench.py\n"; }
 int whisper_bench_ggml_mul_mat(int) { return 0; }
@@ -860,7 +890,7 @@ int whisper_b200_profile_read(int category, char * name, int name_cap, double * 
     if (flops_sampled) *flops_sampled = fl[category];
     return PC_COUNT;
 }
-uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count() + step_launch_count() + enc_attn_launch_count(); }
+uint64_t whisper_b200_kernel_launches(void) { return gemm_launch_count() + kernel_launch_count() + step_launch_count() + enc_attn_launch_count() + vad_launch_count(); }
 void whisper_b200_device_sync(struct whisper_context * ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->model.device);

@@ -105,6 +105,7 @@ State::~State() {
     cudaFree(kv_self.v);
     cudaFree(kv_cross);
     cudaFree(d_qk);
+    vad_state_release(*this);
 }
 
 Context::~Context() {

@@ -155,6 +155,12 @@ struct State {
 
     std::vector<float> mel_host_cache;  // filled by whisper_b200_get_mel
 
+    // VAD (wc:950-965): set by whisper_full / whisper_full_parallel when params.vad, read by the segment-time accessors
+    struct VadMap { int64_t processed, original; };   // centiseconds in the filtered audio -> in the caller's audio
+    bool has_vad_segments = false;
+    std::vector<VadMap> vad_mapping;
+    void * vad_context = nullptr;                      // whisper_vad_context, created on first use, freed with the state
+
     ~State();
 };
 
@@ -197,6 +203,10 @@ bool stage_set_mel(State & st, const float * data, int n_len, int n_mel);
 bool stage_get_mel(State & st, std::vector<float> & out);
 // Encodes one window of each listed state (mel offsets per state) as one batch, then fills their cross caches.
 bool stage_encode(Context & ctx, State * const * states, const int * mel_offsets, int n_states);
+// VAD front end (vad_api.cu)
+bool vad_filter(Context * ctx, State * st, const whisper_full_params & params, const float * samples, int n_samples, std::vector<float> & filtered);
+int64_t vad_map_time(const State & st, int64_t t);
+void vad_state_release(State & st);
 bool stage_conv_probe(Context & ctx, State * st, int mel_offset, float * dst, int64_t cap);  // E1 alone, host dst [T][S]
 
 struct BatchRow {

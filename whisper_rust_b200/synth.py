@@ -323,3 +323,72 @@ def synth_audio(seconds: float, seed: int = 12345, sr: int = SAMPLE_RATE) -> np.
     x += 0.02 * lcg
     x *= 0.8 / max(1e-9, np.max(np.abs(x)))
     return x.astype(np.float32)
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# synthetic Silero-layout VAD checkpoint (reader: whisper.cpp:4775-5098; tensor names whisper-arch.h:181-197)
+# ---------------------------------------------------------------------------------------------------------------------------
+VAD_ENCODER = ((129, 128, 3), (128, 64, 3), (64, 64, 3), (64, 128, 3))   # (in channels, out channels, kernel) of the four conv layers
+
+
+def write_vad_model(out, seed: int = 77, gain: float = 2.0, final_bias: float = -5.7, final_scale: float = 1.2) -> int:
+    """Random-init VAD model in the ggml layout the reference loads.  The STFT basis is a real windowed Fourier basis (258 filters of
+    256 taps: cosines then sines), the conv / LSTM weights are Gaussian; `final_bias` and the positive final-conv weights make quiet
+    windows score below 0.5 and loud ones above, so that gated test audio produces several speech segments."""
+    rng = np.random.default_rng(seed)
+    own = isinstance(out, (str, bytes)) or hasattr(out, "__fspath__")
+    f = open(out, "wb") if own else out
+    n0 = f.tell()
+
+    def tensor(name, arr, f16):
+        a = np.ascontiguousarray(arr, dtype=np.float32)
+        nm = name.encode()
+        f.write(struct.pack("<3i", a.ndim, len(nm), 1 if f16 else 0))
+        f.write(struct.pack(f"<{a.ndim}i", *reversed(a.shape)))
+        f.write(nm)
+        f.write(a.astype("<f2" if f16 else "<f4").tobytes())
+
+    try:
+        f.write(struct.pack("<I", GGML_MAGIC))
+        t = b"silero-16k"
+        f.write(struct.pack("<i", len(t))); f.write(t)
+        f.write(struct.pack("<3i", 5, 1, 2))
+        f.write(struct.pack("<2i", 512, 64))                      # n_window, n_context
+        f.write(struct.pack("<i", len(VAD_ENCODER)))
+        for ic, oc, k in VAD_ENCODER:
+            f.write(struct.pack("<3i", ic, oc, k))
+        f.write(struct.pack("<4i", 128, 128, 128, 1))             # lstm input / hidden, final conv in / out
+        n = np.arange(256)
+        win = 0.5 - 0.5 * np.cos(2 * np.pi * n / 256)
+        k = np.arange(129)[:, None]
+        basis = np.concatenate([np.cos(2 * np.pi * k * n / 256) * win, -np.sin(2 * np.pi * k * n / 256) * win]) / 16.0
+        tensor("_model.stft.forward_basis_buffer", basis.reshape(258, 1, 256), True)
+        for i, (ic, oc, kk) in enumerate(VAD_ENCODER):
+            tensor(f"_model.encoder.{i}.reparam_conv.weight", rng.standard_normal((oc, ic, kk)) * gain / np.sqrt(ic * kk), True)
+            tensor(f"_model.encoder.{i}.reparam_conv.bias", rng.standard_normal(oc) * 0.05, False)
+        tensor("_model.decoder.rnn.weight_ih", rng.standard_normal((512, 128)) * gain / np.sqrt(128), False)
+        tensor("_model.decoder.rnn.weight_hh", rng.standard_normal((512, 128)) * 0.5 / np.sqrt(128), False)
+        tensor("_model.decoder.rnn.bias_ih", rng.standard_normal(512) * 0.1, False)
+        tensor("_model.decoder.rnn.bias_hh", rng.standard_normal(512) * 0.1, False)
+        tensor("_model.decoder.decoder.2.weight", np.abs(rng.standard_normal((1, 128))) * final_scale, True)
+        tensor("_model.decoder.decoder.2.bias", np.array([final_bias]), False)
+        return f.tell() - n0
+    finally:
+        if own:
+            f.close()
+
+
+def vad_model_bytes(**kw) -> bytes:
+    bio = io.BytesIO()
+    write_vad_model(bio, **kw)
+    return bio.getvalue()
+
+
+def gated_audio(seconds: float, seed: int = 12345, period: float = 4.0, duty: float = 0.55, floor: float = 0.002) -> np.ndarray:
+    """synth_audio with alternating loud / near-silent stretches (speech-like gating for the VAD tests)"""
+    a = synth_audio(seconds, seed=seed)
+    t = np.arange(len(a)) / SAMPLE_RATE
+    rng = np.random.default_rng(seed + 1)
+    phase = rng.uniform(0, period)
+    gate = (((t + phase) % period) < duty * period).astype(np.float32)
+    return (a * (floor + (1.0 - floor) * gate)).astype(np.float32)
