@@ -11,7 +11,7 @@ arch = None
 for line in out.splitlines():
     m = re.match(r"\s*Function : (\S+)", line)
     if m:
-        kern = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip().split("(")[0]
+        kern = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip().replace("(anonymous namespace)::", "").split("(")[0]
         hist[kern] = collections.Counter()
         continue
     m = re.match(r"\s*arch = (\S+)", line)
