@@ -45,6 +45,10 @@ WHISPER_API int whisper_b200_decode_batch(struct whisper_context * ctx, struct w
 /* Probes: copy a stage output to host memory.  Return the element count (or -1); copy only when cap is large enough. */
 WHISPER_API int64_t whisper_b200_get_mel(struct whisper_state * state, float * dst, int64_t cap, int * n_len, int * n_len_org, int * n_mel);
 WHISPER_API int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int window, float * dst, int64_t cap);   /* [n_ctx][n_state] */
+/* Grammar engine in isolation (whisper.cpp:5784-5890): start on `rules`, accept the given tokens, write the reject mask of the next step
+ * to mask_out[n_vocab]; returns the number of live grammar stacks */
+WHISPER_API int whisper_b200_test_grammar(struct whisper_context * ctx, const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
+                                          const whisper_token * accept, int n_accept, uint8_t * mask_out);
 /* VAD host-logic test hook: replace the probabilities of a VAD context (so that whisper_vad_segments_from_probs can be checked against
  * the reference on arbitrary sequences, also without a device) */
 WHISPER_API int whisper_b200_test_vad_set_probs(struct whisper_vad_context * vctx, const float * probs, int n);

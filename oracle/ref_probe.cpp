@@ -115,3 +115,19 @@ int ref_probe_dtw_path(const float * cost, int N, int M, int32_t * path_out, int
 }
 
 }
+
+// Grammar (whisper.cpp:5784-5890) in isolation: start the reference's grammar on `rules`, feed it the tokens `accept[0..n_accept)`
+// through whisper_grammar_accept_token, then ask whisper_suppress_invalid_grammar which tokens it penalises next.
+// mask_out[n_vocab] receives 1 for the penalised ids.  Returns the number of grammar stacks alive (0 = the grammar is dead / complete).
+extern "C" int ref_probe_grammar(struct whisper_context * ctx, const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
+                                 const whisper_token * accept, int n_accept, uint8_t * mask_out) {
+    whisper_grammar g = whisper_grammar_init(rules, n_rules, i_start_rule);
+    for (int i = 0; i < n_accept; ++i) whisper_grammar_accept_token(*ctx, g, accept[i]);
+    const int n_vocab = whisper_n_vocab(ctx);
+    std::vector<float> logits((size_t) n_vocab, 0.0f);
+    whisper_full_params p = whisper_full_default_params(WHISPER_SAMPLING_GREEDY);
+    p.grammar_penalty = 1.0f;
+    whisper_suppress_invalid_grammar(*ctx, p, logits, g);
+    for (int i = 0; i < n_vocab; ++i) mask_out[i] = logits[(size_t) i] != 0.0f ? 1 : 0;
+    return (int) g.stacks.size();
+}

@@ -501,29 +501,6 @@ def test_config4_medium_one_hour_clip_sharded(prod_lib, ref_lib):
 
 
 # ---------------------------------------------------------------------------------------------------------------------------
-# an option this library does not implement fails loudly: grammar -> -10 on every entry point.
-# (params.vad is honoured by whisper_full / whisper_full_parallel and ignored by whisper_full_with_state, as in the reference: tests/test_vad.py)
-# ---------------------------------------------------------------------------------------------------------------------------
-def test_grammar_is_refused_not_ignored(prod_lib):
-    ctx = _ctx(prod_lib, "micro", True, RECIPE)
-    st = ctx.create_state()
-    pcm = synth.synth_audio(5.0, seed=5)
-    p = _params(prod_lib, best_of=1)
-    dummy = (C.c_void_p * 1)(C.c_void_p(1))                       # any non-null rule table with n_grammar_rules > 0
-    p.fp.grammar_rules = C.addressof(dummy)
-    p.fp.n_grammar_rules = 1
-    r = prod_lib.whisper_full_with_state(ctx.ptr, st.ptr, p.fp, pcm.ctypes.data_as(C.POINTER(C.c_float)), len(pcm))
-    assert r == -10
-    n = 1
-    r = prod_lib.whisper_b200_full_batch(ctx.ptr, (C.c_void_p * n)(st.ptr), n, p.fp, (C.POINTER(C.c_float) * n)(pcm.ctypes.data_as(C.POINTER(C.c_float))),
-                                         (C.c_int * n)(len(pcm)))
-    assert r == -10
-    p = _params(prod_lib, best_of=1)                               # and the state is still usable afterwards
-    assert st.full(p, pcm) == 0 and st.full_n_segments() >= 1
-    st.free(); ctx.free()
-
-
-# ---------------------------------------------------------------------------------------------------------------------------
 # a real converter-produced checkpoint, when one is present (none ships with this repository: there is no network in the build image)
 # ---------------------------------------------------------------------------------------------------------------------------
 import os  # noqa: E402

@@ -514,12 +514,10 @@ void whisper_reset_timings(struct whisper_context * ctx) {
 // ---------------------------------------------------------------------------------------------
 // full transcription (wc:6795-7864) and result accessors (wc:7866-8033)
 // ---------------------------------------------------------------------------------------------
-// Options this library does not implement fail loudly instead of silently transcribing something else.
+// whisper_full_params options: everything the reference reads on this path is honoured (grammar: grammar.cpp + the sampler's penalty hook).
 static int unsupported_params(const whisper_full_params & params, const char * fn) {
-    if (params.grammar_rules != nullptr && params.n_grammar_rules > 0) {
-        log_error("%s: grammar-constrained sampling (grammar_rules) is not implemented by this library\n", fn);
-        return -10;
-    }
+    (void) params;
+    (void) fn;
     // params.vad is read by whisper_full / whisper_full_parallel only, exactly as in the reference (wc:7720, 7748): whisper_full_with_state
     // itself never looks at it (wc:6795-7711), so a vad = true arriving here transcribes the samples it is given
     return 0;
@@ -1101,6 +1099,23 @@ int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c
     WB_CATCH(3)
 }
 
+
+// Grammar engine in isolation (tests): start a grammar on `rules`, accept the tokens accept[0..n_accept), report the reject mask of the
+// next step (mask_out[n_vocab]).  Returns the number of live stacks.  Host logic only; the context supplies the vocabulary.
+int whisper_b200_test_grammar(struct whisper_context * ctx, const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
+                              const whisper_token * accept, int n_accept, uint8_t * mask_out) {
+    WB_TRY
+    if (!ctx || !rules || !mask_out) return -1;
+    const Vocab & vc = ctx->model.vocab;
+    Grammar g = Grammar::init(rules, n_rules, i_start_rule);
+    for (int i = 0; i < n_accept; ++i)
+        if (accept[i] >= 0 && accept[i] < (int) vc.id_to_token.size()) g.accept_token(vc.id_to_token[(size_t) accept[i]]);
+    std::vector<uint8_t> mask;
+    g.reject_mask(vc.id_to_token, vc.token_eot, mask);
+    memcpy(mask_out, mask.data(), std::min(mask.size(), (size_t) vc.n_vocab));
+    return (int) g.stacks.size();
+    WB_CATCH(-1)
+}
 
 // X1/X2 on caller-supplied HOST data (tests): qk [n_heads][n_tok][T] softmax rows -> cost [n_tok][n_audio] (host copy optional) and, over the
 // rows sot_len .. n_tok-2, the DTW path.  Returns the path length L (path_out[0..L) token indices, [L..2L) time indices), < 0 on failure.

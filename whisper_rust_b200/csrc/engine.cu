@@ -119,6 +119,7 @@ Context::~Context() {
     cudaFree(dec_ws.d_stage);
     if (dec_ws.h_out) cudaFreeHost(dec_ws.h_out);
     cudaFree(dec_ws.d_out);
+    cudaFree(dec_ws.d_grammar);
     cudaFree(d_ahead_slot);
     masks.clear();
     if (stream) cudaStreamDestroy(stream);
@@ -344,6 +345,7 @@ static bool ensure_dec_ws(Context & ctx, int rows, int logit_rows, int max_cells
     cudaFree(ws.d_stage);
     if (ws.h_out) cudaFreeHost(ws.h_out);
     cudaFree(ws.d_out);
+    cudaFree(ws.d_grammar);
     ws = DecWorkspace();
     size_t off = 0;
     auto take = [&](size_t bytes) {
@@ -867,6 +869,31 @@ bool stage_sample(Context & ctx, const SamplerStatic & sst, const SamplerRow * s
     // sampler rows live at the tail of the staging block (the head is still in flight for the decode kernels)
     const size_t o = ws.stage_bytes - (((size_t) n * sizeof(SamplerRow) + 15) & ~(size_t) 15);
     memcpy(ws.h_stage + o, srows, (size_t) n * sizeof(SamplerRow));
+    // grammar-constrained rows: the host computed which tokens the row's grammar rejects (decs[i]->grammar_reject); the mask goes to the
+    // row's slot of a device buffer and the staged sampler row points at it
+    {
+        SamplerRow * hr = (SamplerRow *) (ws.h_stage + o);
+        bool any = false;
+        for (int i = 0; i < n; ++i) any = any || (decs && decs[i] && !decs[i]->grammar_reject.empty());
+        if (any) {
+            if (ws.grammar_rows < ws.logit_rows) {
+                cudaFree(ws.d_grammar);
+                ws.d_grammar = nullptr;
+                WB_CUDA_OK(cudaMalloc((void **) &ws.d_grammar, (size_t) ws.logit_rows * V));
+                ws.grammar_rows = ws.logit_rows;
+            }
+            for (int i = 0; i < n; ++i) {
+                hr[i].grammar_reject = nullptr;
+                if (!decs[i] || decs[i]->grammar_reject.empty()) continue;
+                WB_CHECK((int) decs[i]->grammar_reject.size() == V && srows[i].work_slot < ws.grammar_rows, "grammar mask size\n");
+                uint8_t * dst = ws.d_grammar + (size_t) srows[i].work_slot * V;
+                WB_CUDA_OK(cudaMemcpyAsync(dst, decs[i]->grammar_reject.data(), (size_t) V, cudaMemcpyHostToDevice, s));
+                hr[i].grammar_reject = dst;
+            }
+        } else {
+            for (int i = 0; i < n; ++i) hr[i].grammar_reject = nullptr;
+        }
+    }
     WB_CUDA_OK(cudaMemcpyAsync(ws.d_stage + o, ws.h_stage + o, (size_t) n * sizeof(SamplerRow), cudaMemcpyHostToDevice, s));
     if (prefilter) {
         // the callback mutates HOST logits (wh:474-480): one D2H / H2D round trip per flagged row, only when a callback is set

@@ -15,6 +15,7 @@
 
 #include "gemm_tc.cuh"
 #include "kernels.cuh"
+#include "grammar.h"
 #include "model.h"
 
 namespace wb {
@@ -62,6 +63,8 @@ struct Decoder {
     SamplerOut picked{};  // device-side greedy pick for the current step
     bool want_dists = false;  // copy the distributions to the host after the next sampler launch
     std::mt19937 rng;
+    Grammar grammar;                  // grammar-constrained sampling state (wc:802-808); inactive unless params.grammar_rules is set
+    std::vector<uint8_t> grammar_reject;  // tokens the grammar rejects at the NEXT step (uploaded with the sampler row)
 };
 
 // Encoder activations for up to `windows` 30-second windows processed as one batch of rows.
@@ -101,6 +104,8 @@ struct DecWorkspace {
     SamplerOut * d_out = nullptr;
     int * d_cells = nullptr;       // explicit cell lists [R][max_cells]
     int max_cells = 0;
+    uint8_t * d_grammar = nullptr; // [grammar_rows][V] grammar reject masks, allocated on first use
+    int grammar_rows = 0;
     uint8_t * base = nullptr;
 };
 

@@ -213,6 +213,7 @@ struct BeamCandidate {
     int seek_delta;
     bool has_ts;
     Sequence sequence;
+    Grammar grammar;   // wc:7201
 };
 
 struct Client;
@@ -256,6 +257,8 @@ struct FullJob {
 
     static constexpr int delta_min = 10;
 
+    // grammar rows take the general decoder path: their reject mask is computed on the host every step and uploaded with the sampler row
+    bool has_grammar() const { return params.grammar_rules != nullptr && params.n_grammar_rules > 0; }
     whisper_context * wctx() const { return static_cast<whisper_context *>(ctx); }
     whisper_state * wstate() const { return static_cast<whisper_state *>(st); }
     const Vocab & vocab() const { return ctx->model.vocab; }
@@ -279,6 +282,7 @@ struct FullJob {
     void finish_temperature();
     void emit_results();
     SamplerRow sampler_row(const Decoder & d, int logits_row, bool want_nosp) const;
+    void refresh_grammar_mask(Decoder & d);
     void queue_step_rows();
 };
 
@@ -466,7 +470,16 @@ SamplerRow FullJob::sampler_row(const Decoder & d, int logits_row, bool want_nos
     r.work_slot = logits_row;
     r.suppress = mask->d;
     r.suppress_post = mask->d + vc.n_vocab;
+    r.grammar_reject = nullptr;  // filled in by stage_sample from Decoder::grammar_reject
+    r.grammar_penalty = params.grammar_penalty;
     return r;
+}
+
+// which tokens the decoder's grammar rejects at the step about to be sampled (whisper_suppress_invalid_grammar, wc:5824-5866);
+// empty when the job has no grammar
+void FullJob::refresh_grammar_mask(Decoder & d) {
+    if (params.n_grammar_rules > 0 && d.grammar.active()) d.grammar.reject_mask(vocab().id_to_token, vocab().token_eot, d.grammar_reject);
+    else d.grammar_reject.clear();
 }
 
 // start of one temperature pass (wc:7020-7155): decoder reset, prompt assembly, KV reset, prompt rows
@@ -500,6 +513,11 @@ void FullJob::temp_begin() {
         d.completed = false;
         d.has_ts = false;
         d.want_dists = host_sampling;
+        if (params.grammar_rules != nullptr && params.n_grammar_rules > 0)   // wc:7064-7068
+            d.grammar = Grammar::init(params.grammar_rules, params.n_grammar_rules, params.i_start_rule);
+        else
+            d.grammar = Grammar();
+        d.grammar_reject.clear();
     }
     prompt.clear();
     auto & prompt_past = st->prompt_past;
@@ -526,6 +544,7 @@ void FullJob::temp_begin() {
     sdecs.clear();
     for (int k = 0; k < (int) prompt.size(); ++k) rows.push_back(BatchRow{st, prompt[(size_t) k], k, 0, k == (int) prompt.size() - 1});
     st->decoders[0].i_batch = (int) prompt.size() - 1;
+    refresh_grammar_mask(st->decoders[0]);
     srows.push_back(sampler_row(st->decoders[0], 0, true));
     sdecs.push_back(&st->decoders[0]);
     phase = AFTER_PROMPT;
@@ -582,7 +601,7 @@ void FullJob::step() {
         } else {
             const auto tokens_new = sample_token_topk_host(vc, d, params.beam_search.beam_size);
             for (const auto & token : tokens_new) {
-                bc_per_dec[(size_t) j].push_back({j, d.seek_delta, d.has_ts, d.sequence});
+                bc_per_dec[(size_t) j].push_back({j, d.seek_delta, d.has_ts, d.sequence, d.grammar});
                 bc_per_dec[(size_t) j].back().sequence.tokens.push_back(token);
                 bc_per_dec[(size_t) j].back().sequence.sum_logprobs_all += token.plog;
             }
@@ -608,6 +627,7 @@ void FullJob::step() {
             d.seek_delta = cur.seek_delta;
             d.has_ts = cur.has_ts;
             d.sequence = cur.sequence;
+            d.grammar = cur.grammar;
             st->kv_self.seq_cp(cur.decoder_idx, MAX_DECODERS + j, -1, -1);
         }
         for (int j = 0; j < n_decoders_cur; ++j) {
@@ -640,6 +660,7 @@ void FullJob::step() {
                 result_len = i + 1;
                 has_ts = true;
             }
+            if (d.grammar.active()) d.grammar.accept_token(vc.id_to_token[(size_t) token.id]);  // wc:7329
             if (token.id == vc.token_eot || (params.max_tokens > 0 && i >= params.max_tokens) ||
                 (has_ts && seek + seek_delta + delta_min >= seek_end)) {
                 if (result_len == 0 && !params.no_timestamps) {
@@ -693,6 +714,7 @@ void FullJob::queue_step_rows() {
         if (d.failed || d.completed) continue;
         d.i_batch = (int) rows.size();
         rows.push_back(BatchRow{st, d.sequence.tokens.back().id, n_past, j, true});
+        refresh_grammar_mask(d);
         srows.push_back(sampler_row(d, 0, false));
         sdecs.push_back(&d);
     }
@@ -1497,7 +1519,7 @@ void Scheduler::lane_advance(int lane_id) {
             if (j.phase == FullJob::DONE) continue;
             if (j.phase == FullJob::TEMP_BEGIN) j.temp_begin();
             if ((j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) || j.rows.empty()) continue;
-            if (j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback) has_single = true;
+            if (j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback && !j.has_grammar()) has_single = true;
             else has_multi = true;
         }
         for (FullJob * jp : ln.jobs) {
@@ -1506,7 +1528,7 @@ void Scheduler::lane_advance(int lane_id) {
             any_live = true;
             if (j.phase != FullJob::AFTER_PROMPT && j.phase != FullJob::STEP) continue;
             if (j.rows.empty()) continue;
-            const bool single = j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback;
+            const bool single = j.rows.size() == 1 && j.srows.size() == 1 && !j.params.logits_filter_callback && !j.has_grammar();
             if (has_multi && has_single && single) continue;  // waits for the next iteration
             if (single && (int) ln.rows.size() >= lane_rows) continue;
             // flagged rows of this job map to consecutive logits rows
@@ -1566,7 +1588,10 @@ void Scheduler::lane_advance(int lane_id) {
             }, true);
         };
         const int n_rows = (int) ln.rows.size();
-        const bool fused_step = !any_callback && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) && ln.rows.size() == ln.srows.size();
+        bool any_grammar = false;  // grammar rows carry a host-computed reject mask that only stage_sample uploads
+        for (FullJob * gj : ln.dev_jobs) any_grammar = any_grammar || gj->has_grammar();
+        const bool fused_step = !any_callback && !any_grammar && step_eligible(*ctx, ln.rows.data(), n_rows, any_dists) &&
+                                ln.rows.size() == ln.srows.size();
         bool ok;
         if (fused_step) {
             if (n_rows != ln.last_logged_rows) {

@@ -779,6 +779,31 @@ sampler_kernel(SamplerStatic st, const float * __restrict__ logits_all, int64_t 
     float ts_logprob = -INFINITY;
     if (tsum > 0.0f) ts_logprob = logf(tsum) + ts_max;
     const bool mask_text = ts_logprob > txt_max;
+    // ---- grammar (wc:6334-6355): only when text wins; penalise the rejected tokens, then the log-softmax again over the new logits
+    if (!mask_text && r.grammar_reject != nullptr) {
+        float gmx = -INFINITY;
+        for (int i = tid; i < V; i += SM_THREADS) {
+            float x = lg[i];
+            if (r.grammar_reject[i]) {
+                x = __fsub_rn(x, r.grammar_penalty);
+                lg[i] = x;
+            }
+            gmx = fmaxf(gmx, x);
+        }
+        gmx = block_max(gmx, red);
+        float gs = 0.0f;
+        for (int i = tid; i < V; i += SM_THREADS) {
+            const float x = lg[i];
+            if (x > -INFINITY) gs += expf(x - gmx);
+        }
+        gs = block_sum(gs, red);
+        const float glse = logf(gs) + gmx;
+        for (int i = tid; i < V; i += SM_THREADS) {
+            const float x = lg[i];
+            lp[i] = x > -INFINITY ? x - glse : -INFINITY;
+        }
+        __syncthreads();
+    }
 
     // ---- probs + picks (whisper_compute_probs, whisper_sample_token best=true)
     double sum_ts = 0.0;

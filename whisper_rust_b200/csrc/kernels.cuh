@@ -101,6 +101,9 @@ struct SamplerRow {
     int   pad0;
     const uint8_t * suppress;       // per-row masks (jobs with different suppress rules may share a launch); null: SamplerStatic's
     const uint8_t * suppress_post;
+    const uint8_t * grammar_reject; // null, or [V]: tokens the row's grammar rejects; applied when text beats the timestamps (wc:6334-6355)
+    float grammar_penalty;          // subtracted from the rejected tokens' logits (whisper_full_params.grammar_penalty)
+    int   pad1;
 };
 struct SamplerOut {
     int   id, tid;

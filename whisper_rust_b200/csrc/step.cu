@@ -1641,7 +1641,9 @@ bool stage_step_launch(Context & ctx, int lane, int n_lanes, const BatchRow * ro
     // stream time its kernels inside the real run (graph nodes cannot be bracketed by events without breaking the graph)
     // The sampled step runs with the device to itself (the other lanes are drained first and it is waited for here), so the
     // event pairs bracket each kernel alone -- its own speed, not its share of a machine contended by the other lanes.
-    const bool live_sample = prof_enabled() && (L.step_no[lane]++ % 128) == 7;
+    // every 384th step of a lane is issued live under the profiler (the other lanes are drained for it): ~2 live steps per lane and
+    // bench step, 1.5 % of the timed region (every 128th cost 4 % once the stream API kept all lanes busy all the time)
+    const bool live_sample = prof_enabled() && (L.step_no[lane]++ % 384) == 7;
     if (live_sample)
         for (int l = 0; l < MAX_LANES; ++l)
             if (l != lane && L.stream[l]) WB_CUDA_OK(cudaStreamSynchronize(L.stream[l]));
