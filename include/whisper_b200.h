@@ -98,6 +98,17 @@ WHISPER_API int whisper_b200_test_gemm_wstream(const void * w_f16, const void * 
  * mode 0: out f16 [n][n_out] = f16((x.w^T + bias) * (feature < scale_f1 ? scale : 1));  mode 1: out f32 [n][n_out] += x.w^T + bias */
 WHISPER_API int whisper_b200_test_gemm_wcluster(const void * w_f16, const void * x_f16, void * out, int n, int n_out, int k, const float * bias,
                                                 int mode, float scale, int scale_f1);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The same GEMM as whisper_b200_test_gemm_wstream in its split-K form
+ * (split <= 0: the planner's choice; the partial sums are added in split order, then the bias), all pointers DEVICE memory supplied by
+ * the caller: out f32 [n][n_out] = x f16 [n][k] . w f16 [n_out][k]^T (+ bias f32 [n_out] or NULL), n in 1..256.  The split-K partial sums
+ * live in a fixed 8 MiB array inside the library (2097152 floats; every GPU that loads the library holds it until the process exits), so
+ * the call performs no cudaMalloc / cudaFree and uses no allocating library routine.  Returns 0 with `out` complete (the call
+ * synchronises the default stream it launches on), 1 on a CUDA failure or bad argument, 2 (and logs why) when
+ * splits * n * n_out exceeds 2097152.  All calls on a device share the array: calls that overlap on the GPU race and must be serialised
+ * by the caller. */
+WHISPER_API int whisper_b200_gemm_wstream_noalloc(const void * w_f16, const void * x_f16, float * out, int n, int n_out, int k,
+                                                  const float * bias, int split);
 /* the TMA-streamed decode-step cross attention: same contract as whisper_b200_test_cross_attn */
 WHISPER_API int whisper_b200_test_cross_attn_step(const void * q_f16, const void * kv_f16, void * out_f16, int n_rows, int n_head, int n_ctx);
 /* micro-benchmarks, CUDA-event timed on the launching stream, graph-replayed so that launch overhead is excluded:

@@ -1081,6 +1081,11 @@ int whisper_b200_test_cross_attn_step(const void * q, const void * kv, void * ou
     return test_cross_attn_step((const __half *) q, (const __half *) kv, (__half *) out, n_rows, n_head, n_ctx) ? 0 : 1;
     WB_CATCH(3)
 }
+int whisper_b200_gemm_wstream_noalloc(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int split) {
+    WB_TRY
+    return gemm_wstream_noalloc((const __half *) w, (const __half *) x, out, n, n_out, k, bias, split);
+    WB_CATCH(1)
+}
 int whisper_b200_bench_kernel(const char * kind, int n_rows, int a, int b, int c, int iters, double * us_per_launch, double * bytes_per_launch) {
     WB_TRY
     StepBenchResult r{};

@@ -8,6 +8,7 @@
 #include <array>
 #include <atomic>
 #include <map>
+#include <mutex>
 #include <vector>
 
 #include "log.h"
@@ -2005,5 +2006,83 @@ bool bench_gemm_wcluster(int n_rows, int N_out, int K, int n_weights, int iters,
     }
     cudaFree(w); cudaFree(x); cudaFree(y);
     return ok;
+}
+
+// =============================================================================================
+// gemm_wstream without any allocation (whisper_b200_gemm_wstream_noalloc, include/whisper_b200.h)
+// =============================================================================================
+// The split-K partial sums of gemm_wstream (mode 0) normally live in a cudaMalloc'ed workspace.  Callers that may not allocate get the
+// same GEMM with the partials in a fixed array that is part of the loaded module: every GPU that loads the library holds
+// WS_NOALLOC_MAX_FLOATS * 4 bytes of it until the process exits.  All calls on a device share the array.
+constexpr int64_t WS_NOALLOC_MAX_FLOATS = 2 * 1024 * 1024;  // 8 MiB: split * n * N_out f32 partials
+static __device__ __align__(256) float g_ws_noalloc_partial[WS_NOALLOC_MAX_FLOATS];
+
+// out[t][f] = ((p[0] + p[1]) + ... + p[split-1]) + bias[f]: the summation order of the allocating test entry (test_gemm_wstream)
+__global__ void __launch_bounds__(256)
+ws_noalloc_reduce_kernel(const float * __restrict__ partial, int split, int64_t split_stride, const float * __restrict__ bias, int N_out,
+                         float * __restrict__ out) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < split_stride; i += (int64_t) gridDim.x * blockDim.x) {
+        float acc = partial[i];
+        for (int s = 1; s < split; ++s) acc = __fadd_rn(acc, partial[(int64_t) s * split_stride + i]);
+        if (bias != nullptr) acc = __fadd_rn(acc, __ldg(bias + (int) (i % N_out)));
+        out[i] = acc;
+    }
+}
+
+// The device address of the array, looked up once per device with that device current.  In host code `g_ws_noalloc_partial` is only
+// the host-side handle of the symbol; kernels must be given the address cudaGetSymbolAddress returns.
+static float * ws_noalloc_scratch() {
+    static std::mutex mu;
+    static float * addr[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    if (addr[dev] == nullptr) {
+        void * p = nullptr;
+        const cudaError_t err = cudaGetSymbolAddress(&p, g_ws_noalloc_partial);
+        if (err != cudaSuccess) {
+            log_error("gemm_wstream_noalloc: cudaGetSymbolAddress failed on device %d: %d (%s)\n", dev, (int) err, cudaGetErrorString(err));
+            return nullptr;
+        }
+        addr[dev] = (float *) p;
+    }
+    return addr[dev];
+}
+
+// 0 = done (output complete on return), 1 = CUDA failure or bad argument, 2 = the partials do not fit the fixed array
+int gemm_wstream_noalloc(const __half * w, const __half * x, float * out, int n, int N_out, int K, const float * bias, int force_split) {
+    if (w == nullptr || x == nullptr || out == nullptr || n < 1 || n > 256 || N_out < 1 || K < 1) {
+        log_error("gemm_wstream_noalloc: bad arguments (n %d in 1..256, n_out %d, k %d, non-null w / x / out)\n", n, N_out, K);
+        return 1;
+    }
+    const WsPlan p = ws_plan(n, N_out, K, force_split);
+    const int64_t need = (int64_t) p.split * n * N_out;
+    if (need > WS_NOALLOC_MAX_FLOATS) {
+        log_error("gemm_wstream_noalloc: %d splits x %d rows x %d outputs = %lld partial sums exceed the fixed scratch of %lld floats (%lld MiB); "
+                  "use fewer rows, fewer splits, or the allocating entry point\n",
+                  p.split, n, N_out, (long long) need, (long long) WS_NOALLOC_MAX_FLOATS, (long long) (WS_NOALLOC_MAX_FLOATS * 4 >> 20));
+        return 2;
+    }
+    float * part = ws_noalloc_scratch();
+    if (part == nullptr) return 1;
+    const cudaStream_t s = 0;
+    prof_suspend(true);  // the in-situ profiler would create events for a sampled launch
+    bool ok = cudaMemsetAsync(part, 0, (size_t) need * sizeof(float), s) == cudaSuccess;  // the array keeps the previous call's sums
+    WsOut po{};
+    po.partial = part;
+    int split = 0;
+    ok = ok && gemm_wstream(w, x, n, N_out, K, po, force_split, &split, s, false);
+    if (ok) {
+        const int64_t total = (int64_t) n * N_out;
+        const int blocks = (int) std::min<int64_t>(ceil_div64(total, 256), 148 * 8);
+        ok = launch_k(ws_noalloc_reduce_kernel, dim3(blocks), dim3(256), 0, s, false, (const float *) part, split, total, bias, N_out, out);
+    }
+    prof_suspend(false);
+    const cudaError_t err = cudaStreamSynchronize(s);
+    if (err != cudaSuccess) {
+        log_error("gemm_wstream_noalloc: CUDA error %d (%s)\n", (int) err, cudaGetErrorString(err));
+        return 1;
+    }
+    return ok ? 0 : 1;
 }
 }  // namespace wb

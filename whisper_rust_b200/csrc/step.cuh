@@ -49,5 +49,8 @@ bool test_gemm_wcluster(const __half * w, const __half * x, void * out, int n, i
 bool bench_gemm_wcluster(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out);
 bool bench_overlap_gemm(int n_rows, int N_out, int K, int n_weights, int iters, StepBenchResult * out);
 bool test_cross_attn_step(const __half * q_f16, const __half * kv, __half * out, int n_rows, int H, int T);
+// gemm_wstream with its split-K partial sums in a fixed module-scope device array: no cudaMalloc / cudaFree on any call
+// (0 = done, 1 = failure, 2 = beyond the array's size).  step.cu, end of file.
+int gemm_wstream_noalloc(const __half * w, const __half * x, float * out, int n, int N_out, int K, const float * bias, int force_split);
 
 }  // namespace wb
