@@ -98,6 +98,10 @@ WHISPER_API int whisper_b200_test_gemm_wstream(const void * w_f16, const void * 
  * mode 0: out f16 [n][n_out] = f16((x.w^T + bias) * (feature < scale_f1 ? scale : 1));  mode 1: out f32 [n][n_out] += x.w^T + bias */
 WHISPER_API int whisper_b200_test_gemm_wcluster(const void * w_f16, const void * x_f16, void * out, int n, int n_out, int k, const float * bias,
                                                 int mode, float scale, int scale_f1);
+/* Host only (tests): expand n_elements of a quantised ggml tensor (type ids of ggml.h: 2 q4_0, 3 q4_1, 6 q5_0, 7 q5_1, 8 q8_0, 10..14
+ * q2_K..q6_K) to f32 exactly as the model loader does before rounding to f16 (replaces dequantize_row_*, ggml/src/ggml-quants.c:
+ * 260-420, 706-1720).  Returns 0, or 1 for a type this loader does not expand / a partial block. */
+WHISPER_API int whisper_b200_test_dequantize(int ggml_type, const void * blocks, int64_t n_elements, float * dst);
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under CUDA
  * graph capture, tight serving loops, harnesses that forbid it).  The same GEMM as whisper_b200_test_gemm_wstream in its split-K form
  * (split <= 0: the planner's choice; the partial sums are added in split order, then the bias), all pointers DEVICE memory supplied by

@@ -120,6 +120,37 @@ def blobs():
     return model_blob
 
 
+GGML_TYPE_NAMES = {2: "q4_0", 3: "q4_1", 6: "q5_0", 7: "q5_1", 8: "q8_0", 10: "q2_K", 11: "q3_K", 12: "q4_K", 13: "q5_K", 14: "q6_K"}
+
+
+def ggml_codec(lib):
+    """(quantizer, dequantizer) backed by the reference's own ggml_quantize_chunk / dequantize_row_* (ggml-quants.c) in the oracle
+    library: the block codec synth.write_model takes for the formats it does not pack itself."""
+    lib.ggml_cpu_init()                                                     # the f16 -> f32 table dequantize_row_* reads
+    lib.ggml_quantize_chunk.restype = C.c_size_t
+    lib.ggml_quantize_chunk.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+    lib.ggml_row_size.restype = C.c_size_t
+    lib.ggml_row_size.argtypes = [C.c_int, C.c_int64]
+
+    def quantizer(x, ttype):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        cols = x.shape[-1]
+        rows = x.size // cols
+        buf = np.zeros(lib.ggml_row_size(ttype, cols) * rows, dtype=np.uint8)
+        assert lib.ggml_quantize_chunk(ttype, x.ctypes.data, buf.ctypes.data, 0, rows, cols, None) == buf.size
+        return buf.tobytes()
+
+    def dequantizer(raw, ttype, n):
+        fn = getattr(lib, "dequantize_row_" + GGML_TYPE_NAMES[ttype])
+        fn.restype, fn.argtypes = None, [C.c_void_p, C.c_void_p, C.c_int64]
+        src = np.frombuffer(raw, dtype=np.uint8)
+        out = np.empty(n, dtype=np.float32)
+        fn(src.ctypes.data, out.ctypes.data, n)
+        return out
+
+    return quantizer, dequantizer
+
+
 def ref_mel(lib, st):
     n_len, n_org, n_mel = C.c_int(), C.c_int(), C.c_int()
     p = lib.ref_probe_mel(st.ptr, C.byref(n_len), C.byref(n_org), C.byref(n_mel))

@@ -357,7 +357,7 @@ def test_long_beam_and_fallback_cases_vs_oracle(prod_lib, ref_lib, key):
 # ---------------------------------------------------------------------------------------------------------------------------
 # quantised ggml checkpoints (ftype -> wtype, wc:1567-1577) and shapes with n_audio_layer != n_text_layer
 # ---------------------------------------------------------------------------------------------------------------------------
-from conftest import prod_embd_enc, ref_embd_enc  # noqa: E402
+from conftest import ggml_codec, prod_embd_enc, ref_embd_enc  # noqa: E402
 
 QREC = synth.InitRecipe(te_std=0.2)
 
@@ -396,9 +396,34 @@ def test_quantised_checkpoint_loads_and_matches(prod_lib, ref_lib, arch, ftype):
     assert int(np.argmax(lq)) == int(np.argmax(lr))
 
 
+@pytest.mark.parametrize("ftype", [10, 11, 12, 13, 14])
+def test_k_quantised_checkpoint_loads_and_matches(prod_lib, ref_lib, ftype):
+    """q2_K ... q6_K files (256-element super-blocks; what examples/quantize writes for the *_k types), blocks produced by the
+    reference's own ggml_quantize_chunk.  Same two bars as the legacy formats: (1) bit-identical to the f16 file holding
+    f16(dequantize_row(blocks)) (tests/test_quant_formats.py pins the expansion itself bit for bit on the CPU); (2) against the oracle,
+    which keeps the blocks and quantises the activations to q8_K inside vec_dot: measured on the oracle itself (quantised vs expanded
+    file) 1.0e-2 rel on the encoder output, 1.4e-2 on the logits, up to 0.21 absolute on a logit with top-2 gaps of 0.11-0.60, so the
+    top token is compared only where the reference's own gap clears twice the measured difference."""
+    quantizer, dequantizer = ggml_codec(ref_lib)
+    pcm = synth.synth_audio(30.0, seed=11)
+    blob_q = synth.model_bytes("minik", QREC, ftype=ftype, quantizer=quantizer, dequantizer=dequantizer)
+    blob_x = synth.model_bytes("minik", QREC, ftype=1, expand_ftype=ftype, quantizer=quantizer, dequantizer=dequantizer)
+    eq, lq, ft = _enc_logits(prod_lib, True, blob_q, pcm)
+    ex, lx, _ = _enc_logits(prod_lib, True, blob_x, pcm)
+    assert ft == ftype
+    np.testing.assert_array_equal(eq, ex)
+    np.testing.assert_array_equal(lq, lx)
+    er, lr, _ = _enc_logits(ref_lib, False, blob_q, pcm)
+    print("k-quantised ftype", ftype, "encoder rel err", rel_err(eq, er), "logits rel err", rel_err(lq, lr))
+    assert rel_err(eq, er) < 2e-2 and rel_err(lq, lr) < 3e-2
+    top2 = np.sort(lr)[-2:]
+    if top2[1] - top2[0] > 2.0 * float(np.abs(lq - lr).max()):
+        assert int(np.argmax(lq)) == int(np.argmax(lr))
+
+
 def test_unsupported_quantisation_fails_loudly(prod_lib):
     blob = bytearray(synth.model_bytes("micro", QREC, with_tensors=False))
-    blob[4 + 10 * 4:4 + 11 * 4] = (12).to_bytes(4, "little")       # ftype 12 = Q3_K: a 256-wide K-quant
+    blob[4 + 10 * 4:4 + 11 * 4] = (19).to_bytes(4, "little")       # ftype 19 = IQ4_NL: a codebook type, not expanded by the loader
     with pytest.raises(Exception):
         WhisperContext.new_from_buffer_with_params(bytes(blob), WhisperContextParameters(use_gpu=True), lib=prod_lib)
 

@@ -1081,6 +1081,13 @@ int whisper_b200_test_cross_attn_step(const void * q, const void * kv, void * ou
     return test_cross_attn_step((const __half *) q, (const __half *) kv, (__half *) out, n_rows, n_head, n_ctx) ? 0 : 1;
     WB_CATCH(3)
 }
+// Host only: the loader's expansion of a quantised ggml tensor (model.cpp: dequantize_blocks) on caller data.  0 = done, 1 = type not
+// expanded by this loader or n not a whole number of blocks.
+int whisper_b200_test_dequantize(int ggml_type, const void * blocks, int64_t n_elements, float * dst) {
+    WB_TRY
+    return dequantize_tensor(ggml_type, blocks, n_elements, dst) ? 0 : 1;
+    WB_CATCH(1)
+}
 int whisper_b200_gemm_wstream_noalloc(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int split) {
     WB_TRY
     return gemm_wstream_noalloc((const __half *) w, (const __half *) x, out, n, n_out, k, bias, split);

@@ -80,8 +80,10 @@ enum class Kind { F32_VEC, F16_MAT, CONV1, CONV2 };
 // ggml/src/ggml-quants.c).  The B200 path computes in f16 x f16 -> f32: a quantised matrix is expanded ONCE at load,
 // x = q * d (+ m) evaluated in f32 like dequantize_row_*, then rounded to f16.  (The reference instead keeps the blocks and
 // quantises the ACTIVATIONS to q8_0/q8_1 inside vec_dot, so agreement with it on such checkpoints is tolerance-level.)
-enum : int { GT_F32 = 0, GT_F16 = 1, GT_Q4_0 = 2, GT_Q4_1 = 3, GT_Q5_0 = 6, GT_Q5_1 = 7, GT_Q8_0 = 8 };
-static constexpr int QK = 32;   // elements per block, all five legacy types
+enum : int { GT_F32 = 0, GT_F16 = 1, GT_Q4_0 = 2, GT_Q4_1 = 3, GT_Q5_0 = 6, GT_Q5_1 = 7, GT_Q8_0 = 8,
+             GT_Q2_K = 10, GT_Q3_K = 11, GT_Q4_K = 12, GT_Q5_K = 13, GT_Q6_K = 14 };
+static constexpr int QK = 32;     // elements per block, the five legacy types
+static constexpr int QK_K = 256;  // elements per super-block, the five K types
 
 static int ftype_to_wtype(int ftype) {  // ggml_ftype_to_ggml_type (ggml.c); -1: not supported here
     switch (ftype) {
@@ -92,7 +94,12 @@ static int ftype_to_wtype(int ftype) {  // ggml_ftype_to_ggml_type (ggml.c); -1:
         case 7: return GT_Q8_0;
         case 8: return GT_Q5_0;
         case 9: return GT_Q5_1;
-        default: return -1;   // 4 (Q4_1_SOME_F16) is rejected by ggml itself; 10+ are the 256-wide K-quants / IQ types
+        case 10: return GT_Q2_K;
+        case 11: return GT_Q3_K;
+        case 12: return GT_Q4_K;
+        case 13: return GT_Q5_K;
+        case 14: return GT_Q6_K;
+        default: return -1;   // 4 (Q4_1_SOME_F16) is rejected by ggml itself; 15+ are the codebook (IQ) types and bf16
     }
 }
 static size_t quant_block_bytes(int t) {
@@ -102,10 +109,107 @@ static size_t quant_block_bytes(int t) {
         case GT_Q5_0: return 2 + 4 + 16;
         case GT_Q5_1: return 4 + 4 + 16;
         case GT_Q8_0: return 2 + 32;
+        case GT_Q2_K: return 16 + 64 + 4;            // scales | qs | d dmin
+        case GT_Q3_K: return 32 + 64 + 12 + 2;       // hmask | qs | scales | d
+        case GT_Q4_K: return 4 + 12 + 128;           // d dmin | scales | qs
+        case GT_Q5_K: return 4 + 12 + 32 + 128;      // d dmin | scales | qh | qs
+        case GT_Q6_K: return 128 + 64 + 16 + 2;      // ql | qh | scales | d
         default: return 0;
     }
 }
+static int quant_block_elems(int t) { return t >= GT_Q2_K && t <= GT_Q6_K ? QK_K : QK; }
+
+// One 256-element super-block of a K type (block_q{2,3,4,5,6}_K, ggml-common.h:252-325; dequantize_row_q*_K, ggml-quants.c:706-1720).
+// Every K type is "sixteen groups of 16 elements, each with a scale (and, for q2/q4/q5, a minimum)": the block is first unpacked into
+// integer levels and per-group f32 scale / minimum, then y = scale * level (- minimum) in the reference's order of operations.
+static inline uint16_t rd16(const uint8_t * p) {
+    uint16_t v;
+    memcpy(&v, p, 2);
+    return v;
+}
+// the 6-bit (scale, minimum) pair k of the 12-byte table q4_K / q5_K share (get_scale_min_k4, ggml-quants.c:625-632)
+static inline void scale_min_6bit(const uint8_t * tab, int k, int & sc, int & mn) {
+    if (k < 4) {
+        sc = tab[k] & 63;
+        mn = tab[k + 4] & 63;
+    } else {
+        sc = (tab[k + 4] & 0x0F) | ((tab[k - 4] >> 6) << 4);
+        mn = (tab[k + 4] >> 4) | ((tab[k] >> 6) << 4);
+    }
+}
+static void expand_k_block(int t, const uint8_t * p, float * y) {
+    int level[QK_K];
+    float scale[16], minimum[16];
+    bool has_min = false;
+    if (t == GT_Q2_K || t == GT_Q3_K) {
+        // 2-bit planes: element e of half hf (128 elements) and plane pl (32 elements) sits in byte qs[hf * 32 + e % 32], bits 2 pl
+        const uint8_t * qs = p + (t == GT_Q2_K ? 16 : 32);
+        for (int e = 0; e < QK_K; ++e) level[e] = (qs[(e >> 7) * 32 + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+        if (t == GT_Q2_K) {
+            const float d = h2f(rd16(p + 80)), dmin = h2f(rd16(p + 82));
+            for (int g = 0; g < 16; ++g) {
+                scale[g] = d * (float) (p[g] & 0x0F);
+                minimum[g] = dmin * (float) (p[g] >> 4);
+            }
+            has_min = true;
+        } else {
+            // third bit: hmask[e % 32] bit e / 32, CLEAR means "subtract 4"; 6-bit scales: low nibbles in bytes 0..7, top two bits in 8..11
+            for (int e = 0; e < QK_K; ++e)
+                if (!((p[e & 31] >> (e >> 5)) & 1)) level[e] -= 4;
+            const uint8_t * tab = p + 96;
+            const float d = h2f(rd16(p + 108));
+            for (int g = 0; g < 16; ++g) {
+                const int lo = g < 8 ? (tab[g] & 0x0F) : (tab[g - 8] >> 4);
+                const int hi = (tab[8 + (g & 3)] >> (2 * (g >> 2))) & 3;
+                scale[g] = d * (float) ((lo | (hi << 4)) - 32);
+            }
+        }
+    } else if (t == GT_Q4_K || t == GT_Q5_K) {
+        // nibbles: chunk c (64 elements) uses bytes qs[c * 32 ..): low nibbles first, then high nibbles; q5_K adds bit e / 32 of qh[e % 32]
+        const uint8_t * qs = p + (t == GT_Q4_K ? 16 : 48);
+        for (int e = 0; e < QK_K; ++e) {
+            const uint8_t b = qs[(e >> 6) * 32 + (e & 31)];
+            level[e] = (e & 32) ? (b >> 4) : (b & 0x0F);
+        }
+        if (t == GT_Q5_K)
+            for (int e = 0; e < QK_K; ++e)
+                if ((p[16 + (e & 31)] >> (e >> 5)) & 1) level[e] += 16;
+        const float d = h2f(rd16(p)), dmin = h2f(rd16(p + 2));
+        for (int k = 0; k < 8; ++k) {   // eight groups of 32 = pairs of 16-element groups
+            int sc, mn;
+            scale_min_6bit(p + 4, k, sc, mn);
+            scale[2 * k] = scale[2 * k + 1] = d * (float) sc;
+            minimum[2 * k] = minimum[2 * k + 1] = dmin * (float) mn;
+        }
+        has_min = true;
+    } else {  // GT_Q6_K
+        // per half (128 elements, 64 bytes of ql, 32 of qh): quarter qt of the half takes nibble qt / 2 of ql[e % 32 + 32 (qt & 1)] and
+        // bits 2 qt of qh[e % 32]; levels are offset by 32; int8 scales
+        const uint8_t * ql = p, * qh = p + 128;
+        const int8_t * sc = (const int8_t *) (p + 192);
+        const float d = h2f(rd16(p + 208));
+        for (int e = 0; e < QK_K; ++e) {
+            const int hf = e >> 7, qt = (e >> 5) & 3, l = e & 31;
+            const uint8_t b = ql[hf * 64 + l + 32 * (qt & 1)];
+            const int lo = (qt & 2) ? (b >> 4) : (b & 0x0F);
+            const int hi = (qh[hf * 32 + l] >> (2 * qt)) & 3;
+            level[e] = (lo | (hi << 4)) - 32;
+        }
+        for (int g = 0; g < 16; ++g) scale[g] = d * (float) sc[g];
+    }
+    if (has_min) {
+        for (int e = 0; e < QK_K; ++e) y[e] = scale[e >> 4] * (float) level[e] - minimum[e >> 4];
+    } else {
+        for (int e = 0; e < QK_K; ++e) y[e] = scale[e >> 4] * (float) level[e];
+    }
+}
+
 static void dequantize_blocks(int t, const uint8_t * src, int64_t n, float * dst) {
+    if (quant_block_elems(t) == QK_K) {
+        const size_t kbs = quant_block_bytes(t);
+        for (int64_t b = 0; b < n / QK_K; ++b) expand_k_block(t, src + (size_t) b * kbs, dst + b * QK_K);
+        return;
+    }
     const int64_t nb = n / QK;
     const size_t bs = quant_block_bytes(t);
     for (int64_t b = 0; b < nb; ++b) {
@@ -165,6 +269,13 @@ struct Dest {
 
 }  // namespace
 
+// the loader's block expansion alone (tests): n elements of ggml type `ggml_type` -> f32; false for a type the loader does not expand
+bool dequantize_tensor(int ggml_type, const void * blocks, int64_t n, float * dst) {
+    if (quant_block_bytes(ggml_type) == 0 || n < 0 || (n % quant_block_elems(ggml_type)) != 0 || !blocks || !dst) return false;
+    dequantize_blocks(ggml_type, (const uint8_t *) blocks, n, dst);
+    return true;
+}
+
 bool load_model(whisper_model_loader * loader, int device, Model & m) {
     Reader rd{loader};
     m.device = device;
@@ -198,8 +309,8 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     (void) qntvr;
     const int wtype = ftype_to_wtype(hp.ftype);  // wc:1567-1577
     if (wtype < 0) {
-        log_error("%s: invalid model (bad ftype value %d): supported are f32, f16, q4_0, q4_1, q5_0, q5_1, q8_0 (the 256-wide K-quants "
-                  "are not expanded by this loader)\n", __func__, hp.ftype);
+        log_error("%s: invalid model (bad ftype value %d): supported are f32, f16, q4_0, q4_1, q5_0, q5_1, q8_0, q2_K, q3_K, q4_K, q5_K, "
+                  "q6_K (the codebook IQ types and bf16 are not expanded by this loader)\n", __func__, hp.ftype);
         return false;
     }
     const int S = hp.n_audio_state, H = hp.n_audio_head, T = hp.n_audio_ctx, M = hp.n_mels, V = hp.n_vocab;
@@ -466,13 +577,13 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
             log_error("%s: tensor '%s' has wrong size in model file: expected f32 data\n", __func__, name.c_str());
             return false;
         }
-        if (qbs != 0 && (d.kind != Kind::F16_MAT || ttype != wtype || (ne[0] % QK) != 0)) {
+        if (qbs != 0 && (d.kind != Kind::F16_MAT || ttype != wtype || (ne[0] % quant_block_elems(ttype)) != 0)) {
             // the reference sizes every matrix by the file's wtype and the conv kernels by f16 (wc:1696): anything else is
             // "wrong size in model file" there too
             log_error("%s: tensor '%s' has wrong size in model file (type %d, model wtype %d)\n", __func__, name.c_str(), ttype, wtype);
             return false;
         }
-        const size_t file_bytes = qbs != 0 ? (size_t) (nelements / QK) * qbs : (size_t) nelements * (ttype == GT_F16 ? 2 : 4);
+        const size_t file_bytes = qbs != 0 ? (size_t) (nelements / quant_block_elems(ttype)) * qbs : (size_t) nelements * (ttype == GT_F16 ? 2 : 4);
         buf.resize(file_bytes);
         if (!rd.read(buf.data(), buf.size())) {
             log_error("%s: tensor '%s' is truncated\n", __func__, name.c_str());

@@ -67,6 +67,8 @@ ARCHS = {
     "distil":   Arch("distil", 51865, 1500, 192, 3, 4, 448, 192, 3, 2, 80),
     "micro":    Arch("micro", 51865, 1500, 128, 2, 2, 448, 128, 2, 2, 80),
     "mini":     Arch("mini", 51865, 1500, 192, 3, 2, 448, 192, 3, 3, 80),
+    # every row length a multiple of 256: the smallest shape the K-quant block formats (q2_K ... q6_K) can hold
+    "minik":    Arch("minik", 51865, 1500, 256, 4, 2, 448, 256, 4, 3, 80),
 }
 
 
@@ -163,7 +165,11 @@ class InitRecipe:
 
 # ---- quantised checkpoints (examples/quantize: ggml_common_quantize_0 quantises the 2-D matrices, leaves the 3-D conv kernels f16 and
 # the 1-D / positional tensors f32).  Block layouts: ggml/src/ggml-common.h; the arithmetic follows quantize_row_*_ref (ggml-quants.c).
-FTYPE_TO_TTYPE = {2: 2, 3: 3, 7: 8, 8: 6, 9: 7}     # ggml_ftype -> ggml_type: q4_0, q4_1, q8_0, q5_0, q5_1
+FTYPE_TO_TTYPE = {2: 2, 3: 3, 7: 8, 8: 6, 9: 7,     # ggml_ftype -> ggml_type: q4_0, q4_1, q8_0, q5_0, q5_1
+                  10: 10, 11: 11, 12: 12, 13: 13, 14: 14}   # q2_K, q3_K, q4_K, q5_K, q6_K (256-element super-blocks)
+# This module packs q8_0 / q4_0 / q5_0 itself.  For the other types write_model takes the block codec from its caller:
+#   quantizer(x: f32 array, ggml_type) -> bytes      dequantizer(raw: bytes, ggml_type, n) -> f32 array of n elements
+# (the tests pass the reference's own ggml_quantize_chunk / dequantize_row_* through the oracle library).
 
 
 def _quantize(x: np.ndarray, ttype: int) -> bytes:
@@ -225,7 +231,7 @@ def _dequantize(raw: bytes, ttype: int, n: int) -> np.ndarray:
 
 
 def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype: int = 1, with_tensors: bool = True,
-                expand_ftype: int | None = None) -> int:
+                expand_ftype: int | None = None, quantizer=None, dequantizer=None) -> int:
     """Write a random-init model to `out` (path or binary file object). Returns bytes written.
 
     with_tensors=False writes the reference's own test convention: a header-only file with
@@ -267,10 +273,16 @@ def write_model(arch: str | Arch, out, recipe: InitRecipe = InitRecipe(), ftype:
                 if expand_ftype is not None and kind in ("w", "te"):
                     # the f16 checkpoint a quantised one expands to: x = f16(dequantize(quantize(x))) (what the B200 loader keeps)
                     qt0 = FTYPE_TO_TTYPE[expand_ftype]
-                    x = _dequantize(_quantize(x, qt0), qt0, n).reshape(shape)
+                    if quantizer is not None and dequantizer is not None:
+                        x = np.asarray(dequantizer(quantizer(x, qt0), qt0, n), dtype=np.float32).reshape(shape)
+                    else:
+                        x = _dequantize(_quantize(x, qt0), qt0, n).reshape(shape)
                 f16 = (ftype == 1 and kind in ("w", "cw", "te")) or (ftype >= 2 and kind == "cw")
                 qt = FTYPE_TO_TTYPE[ftype] if ftype >= 2 and kind in ("w", "te") else None
-                payload = _quantize(x, qt) if qt is not None else x.astype("<f2" if f16 else "<f4").tobytes()
+                if qt is not None:
+                    payload = quantizer(x, qt) if quantizer is not None else _quantize(x, qt)
+                else:
+                    payload = x.astype("<f2" if f16 else "<f4").tobytes()
                 nm = name.encode()
                 f.write(struct.pack("<3i", len(shape), len(nm), qt if qt is not None else (1 if f16 else 0)))
                 f.write(struct.pack(f"<{len(shape)}i", *reversed(shape)))
