@@ -49,6 +49,11 @@ WHISPER_API int64_t whisper_b200_get_embd_enc(struct whisper_context * ctx, int 
  * to mask_out[n_vocab]; returns the number of live grammar stacks */
 WHISPER_API int whisper_b200_test_grammar(struct whisper_context * ctx, const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
                                           const whisper_token * accept, int n_accept, uint8_t * mask_out);
+/* the same automaton on a caller-supplied vocabulary (token_texts[n_vocab], NUL-terminated strings; ids >= token_eot are never
+ * rejected, wc:5830-5840): host only, needs neither a context nor a device */
+WHISPER_API int whisper_b200_test_grammar_vocab(const char * const * token_texts, int n_vocab, int token_eot,
+                                                const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
+                                                const whisper_token * accept, int n_accept, uint8_t * mask_out);
 /* VAD host-logic test hook: replace the probabilities of a VAD context (so that whisper_vad_segments_from_probs can be checked against
  * the reference on arbitrary sequences, also without a device) */
 WHISPER_API int whisper_b200_test_vad_set_probs(struct whisper_vad_context * vctx, const float * probs, int n);

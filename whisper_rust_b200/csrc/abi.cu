@@ -1129,6 +1129,24 @@ int whisper_b200_test_grammar(struct whisper_context * ctx, const whisper_gramma
     WB_CATCH(-1)
 }
 
+// The same on a caller-supplied vocabulary (token_texts[n_vocab], NUL-terminated): no context, no device; the CPU suite checks the
+// automaton against the reference with it.
+int whisper_b200_test_grammar_vocab(const char * const * token_texts, int n_vocab, int token_eot, const whisper_grammar_element ** rules,
+                                    size_t n_rules, size_t i_start_rule, const whisper_token * accept, int n_accept, uint8_t * mask_out) {
+    WB_TRY
+    if (!token_texts || n_vocab <= 0 || !rules || !mask_out) return -1;
+    std::vector<std::string> id_to_token((size_t) n_vocab);
+    for (int i = 0; i < n_vocab; ++i) id_to_token[(size_t) i] = token_texts[i] ? token_texts[i] : "";
+    Grammar g = Grammar::init(rules, n_rules, i_start_rule);
+    for (int i = 0; i < n_accept; ++i)
+        if (accept[i] >= 0 && accept[i] < n_vocab) g.accept_token(id_to_token[(size_t) accept[i]]);
+    std::vector<uint8_t> mask;
+    g.reject_mask(id_to_token, token_eot, mask);
+    memcpy(mask_out, mask.data(), std::min(mask.size(), (size_t) n_vocab));
+    return (int) g.stacks.size();
+    WB_CATCH(-1)
+}
+
 // X1/X2 on caller-supplied HOST data (tests): qk [n_heads][n_tok][T] softmax rows -> cost [n_tok][n_audio] (host copy optional) and, over the
 // rows sot_len .. n_tok-2, the DTW path.  Returns the path length L (path_out[0..L) token indices, [L..2L) time indices), < 0 on failure.
 int whisper_b200_test_dtw(const float * qk, int n_heads, int n_tok, int T, int n_audio, int medfilt_width, int sot_len, float * cost_out,
