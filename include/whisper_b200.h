@@ -54,6 +54,10 @@ WHISPER_API int whisper_b200_test_grammar(struct whisper_context * ctx, const wh
 WHISPER_API int whisper_b200_test_grammar_vocab(const char * const * token_texts, int n_vocab, int token_eot,
                                                 const whisper_grammar_element ** rules, size_t n_rules, size_t i_start_rule,
                                                 const whisper_token * accept, int n_accept, uint8_t * mask_out);
+/* the tokenizer (replaces wc:3288-3336) on a caller-supplied vocabulary, n_texts strings per call: host only.  tokens[k * n_max_tokens ...)
+ * and counts[k] are what whisper_tokenize(ctx, texts[k], ..., n_max_tokens) writes and returns.  Returns 0. */
+WHISPER_API int whisper_b200_test_tokenize_vocab(const char * const * token_texts, int n_vocab, const char * const * texts, int n_texts,
+                                                 whisper_token * tokens, int n_max_tokens, int * counts);
 /* VAD host-logic test hook: replace the probabilities of a VAD context (so that whisper_vad_segments_from_probs can be checked against
  * the reference on arbitrary sequences, also without a device) */
 WHISPER_API int whisper_b200_test_vad_set_probs(struct whisper_vad_context * vctx, const float * probs, int n);

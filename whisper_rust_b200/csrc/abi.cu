@@ -5,7 +5,6 @@
 #include <string.h>
 
 #include <atomic>
-#include <regex>
 #include <thread>
 
 #include "../../include/whisper_b200.h"
@@ -337,39 +336,59 @@ int whisper_decode(struct whisper_context * ctx, const whisper_token * tokens, i
 // ---------------------------------------------------------------------------------------------
 // F6: tokenizer (wc:3288-3336, 3973-3988): GPT-2 style regex pre-split, then greedy longest match
 // ---------------------------------------------------------------------------------------------
-static std::vector<int> tokenize_text(const Vocab & vocab, const std::string & text) {
-    std::vector<std::string> words;
-    {
-        std::string str = text;
-        const std::string pat = R"('s|'t|'re|'ve|'m|'ll|'d| ?[[:alpha:]]+| ?[[:digit:]]+| ?[^\s[:alpha:][:digit:]]+|\s+(?!\S)|\s+)";
-        std::regex re(pat);
-        std::smatch m;
-        while (std::regex_search(str, m, re)) {
-            for (auto x : m) words.push_back(x);
-            str = m.suffix();
+// Pre-split.  The reference runs std::regex over
+//   's|'t|'re|'ve|'m|'ll|'d| ?[[:alpha:]]+| ?[[:digit:]]+| ?[^\s[:alpha:][:digit:]]+|\s+(?!\S)|\s+
+// (ECMAScript: leftmost match, first alternative that succeeds, "C" locale classes on bytes).  Every byte belongs to exactly one of four
+// classes, so a match always starts at the current position and the pattern is a small scanner: a contraction suffix; else an optional
+// single ' ' glued to a run of one non-space class; else a whitespace run, which keeps its last character for the next piece unless it
+// reaches the end of the text or is a single character.  Returns the length of the piece starting at s[p] (p < n).
+enum : int { CH_SPACE = 0, CH_ALPHA = 1, CH_DIGIT = 2, CH_OTHER = 3 };
+static inline int char_class(unsigned char c) {
+    if (c == ' ' || (c >= 9 && c <= 13)) return CH_SPACE;
+    if ((c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z')) return CH_ALPHA;
+    if (c >= '0' && c <= '9') return CH_DIGIT;
+    return CH_OTHER;   // punctuation, control characters, every byte of a multi-byte UTF-8 sequence
+}
+static size_t presplit_piece(const char * s, size_t p, size_t n) {
+    if (s[p] == '\'' && p + 1 < n) {
+        static const char * const suffix[] = {"s", "t", "re", "ve", "m", "ll", "d"};
+        for (const char * suf : suffix) {
+            const size_t len = strlen(suf);
+            if (p + 1 + len <= n && memcmp(s + p + 1, suf, len) == 0) return 1 + len;
         }
     }
+    size_t q = p;
+    if (s[q] == ' ' && q + 1 < n && char_class((unsigned char) s[q + 1]) != CH_SPACE) ++q;   // " ?" binds only in front of a run
+    const int cls = char_class((unsigned char) s[q]);
+    if (cls != CH_SPACE) {
+        while (q < n && char_class((unsigned char) s[q]) == cls) ++q;
+        return q - p;
+    }
+    while (q < n && char_class((unsigned char) s[q]) == CH_SPACE) ++q;
+    const size_t run = q - p;
+    return (q == n || run == 1) ? run : run - 1;
+}
+
+static std::vector<int> tokenize_text(const Vocab & vocab, const std::string & text) {
     std::vector<int> tokens;
-    for (const auto & word : words) {
-        if (word.empty()) continue;
-        int i = 0;
-        const int n = (int) word.size();
-        while (i < n) {
-            int j = n;
-            bool found = false;
-            while (j > i) {
-                auto it = vocab.token_to_id.find(word.substr((size_t) i, (size_t) (j - i)));
+    const size_t n = text.size();
+    for (size_t p = 0; p < n;) {
+        const size_t end = p + presplit_piece(text.data(), p, n);
+        // greedy longest match inside the piece (wc:3307-3331); a byte no token starts with is reported and skipped
+        while (p < end) {
+            size_t j = end;
+            for (; j > p; --j) {
+                auto it = vocab.token_to_id.find(text.substr(p, j - p));
                 if (it != vocab.token_to_id.end()) {
                     tokens.push_back(it->second);
-                    i = j;
-                    found = true;
                     break;
                 }
-                --j;
             }
-            if (!found) {
+            if (j == p) {
                 log_error("unknown token\n");
-                ++i;
+                ++p;
+            } else {
+                p = j;
             }
         }
     }
@@ -386,6 +405,27 @@ int whisper_tokenize(struct whisper_context * ctx, const char * text, whisper_to
     }
     for (int i = 0; i < (int) res.size(); i++) tokens[i] = res[(size_t) i];
     return (int) res.size();
+    WB_CATCH(-1)
+}
+// host only (tests): the tokenizer on a caller-supplied id -> text table (later ids win on duplicate texts, like the loader's map).
+// texts[k] -> tokens[k * n_max_tokens ...), counts[k] = whisper_tokenize's return value for that text.
+int whisper_b200_test_tokenize_vocab(const char * const * token_texts, int n_vocab, const char * const * texts, int n_texts, whisper_token * tokens,
+                                     int n_max_tokens, int * counts) {
+    WB_TRY
+    if (!token_texts || n_vocab <= 0 || !texts || n_texts < 0 || !counts || n_max_tokens < 0) return -1;
+    Vocab vocab;
+    for (int i = 0; i < n_vocab; ++i)
+        if (token_texts[i]) vocab.token_to_id[token_texts[i]] = i;
+    for (int k = 0; k < n_texts; ++k) {
+        const auto res = tokenize_text(vocab, texts[k] ? texts[k] : "");
+        if (n_max_tokens < (int) res.size()) {
+            counts[k] = -(int) res.size();
+            continue;
+        }
+        for (int i = 0; i < (int) res.size(); i++) tokens[(size_t) k * n_max_tokens + i] = res[(size_t) i];
+        counts[k] = (int) res.size();
+    }
+    return 0;
     WB_CATCH(-1)
 }
 int whisper_token_count(struct whisper_context * ctx, const char * text) { return -whisper_tokenize(ctx, text, NULL, 0); }
