@@ -59,6 +59,42 @@ def test_segment_rules_equal_the_reference(prod_lib, ref_lib):
     ref.free(); prod.free()
 
 
+def test_segment_rules_equal_the_reference_on_random_runs_and_parameters(prod_lib, ref_lib):
+    """the same, fuzzed: telegraph-like probability tracks (speech / silence runs of random lengths, levels hovering around the two
+    thresholds, single-window spikes and drop-outs) under randomly drawn parameters, incl. the max-speech splitting rules"""
+    ref, prod = vh.Vad(ref_lib), vh.Vad(prod_lib)
+    rng = np.random.default_rng(17)
+    n_seg, n_cases, n_split = 0, 0, 0
+    for k in range(120):
+        n = int(rng.integers(1, 700))
+        track = np.empty(0, dtype=np.float32)
+        while len(track) < n:
+            speech = rng.random() < 0.55
+            run = int(rng.integers(1, 4)) if rng.random() < 0.2 else int(rng.integers(4, 120))
+            level = rng.uniform(0.45, 1.0) if speech else rng.uniform(0.0, 0.55)
+            seg = level + rng.normal(0, rng.choice([0.0, 0.02, 0.1]), run)
+            track = np.concatenate([track, np.clip(seg, 0, 1).astype(np.float32)])
+        p = track[:n]
+        _ref_set_probs(ref_lib, ref, p)
+        _set_probs(prod_lib, prod, p)
+        for _ in range(4):
+            kw = dict(threshold=float(rng.choice([0.2, 0.35, 0.5, 0.5, 0.65, 0.9])),
+                      min_speech_duration_ms=int(rng.choice([0, 32, 100, 250, 600])),
+                      min_silence_duration_ms=int(rng.choice([0, 32, 100, 300, 1000])),
+                      max_speech_duration_s=float(rng.choice([0.5, 1.0, 2.5, 6.0, 1e9])),
+                      speech_pad_ms=int(rng.choice([0, 30, 100, 500])),
+                      samples_overlap=float(rng.choice([0.0, 0.1, 0.5])))
+            want = ref.segments(_params(ref_lib, **kw))
+            got = prod.segments(_params(prod_lib, **kw))
+            assert got == want, (k, n, kw)
+            n_seg += len(want)
+            n_cases += 1
+            n_split += int(kw["max_speech_duration_s"] < 3.0 and len(want) > 1)
+    print("vad fuzz:", n_cases, "cases", n_seg, "segments", n_split, "split cases")
+    assert n_cases == 480 and n_seg > 500 and n_split > 20
+    ref.free(); prod.free()
+
+
 def _ref_set_probs(ref_lib, ref, p):
     """give the reference an arbitrary probability sequence: run detect_speech on len(p) windows of silence, then overwrite the
     probabilities it holds (whisper_vad_probs returns its own buffer)"""
