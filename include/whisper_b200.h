@@ -107,6 +107,13 @@ WHISPER_API int whisper_b200_test_gemm_wstream(const void * w_f16, const void * 
  * mode 0: out f16 [n][n_out] = f16((x.w^T + bias) * (feature < scale_f1 ? scale : 1));  mode 1: out f32 [n][n_out] += x.w^T + bias */
 WHISPER_API int whisper_b200_test_gemm_wcluster(const void * w_f16, const void * x_f16, void * out, int n, int n_out, int k, const float * bias,
                                                 int mode, float scale, int scale_f1);
+/* Host logic of whisper_vad without a device (tests; replaces wc:6643-6790 and map_processed_to_original_time wc:7882-7925): segments
+ * from the context's current probabilities, then the sample filter (out[cap]) and the time-mapping table (table[2 * table_cap] as
+ * (processed, original) centisecond pairs, *n_table entries); map_in[n_map] -> map_out through that table.  Returns the number of
+ * filtered samples or -1. */
+WHISPER_API int whisper_b200_test_vad_filter(struct whisper_vad_context * vctx, struct whisper_vad_params params, const float * samples,
+                                             int n_samples, float * out, int cap, int64_t * table, int table_cap, int * n_table,
+                                             const int64_t * map_in, int64_t * map_out, int n_map);
 /* Host only (tests): expand n_elements of a quantised ggml tensor (type ids of ggml.h: 2 q4_0, 3 q4_1, 6 q5_0, 7 q5_1, 8 q8_0, 10..14
  * q2_K..q6_K) to f32 exactly as the model loader does before rounding to f16 (replaces dequantize_row_*, ggml/src/ggml-quants.c:
  * 260-420, 706-1720).  Returns 0, or 1 for a type this loader does not expand / a partial block. */

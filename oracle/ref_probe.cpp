@@ -131,3 +131,26 @@ extern "C" int ref_probe_grammar(struct whisper_context * ctx, const whisper_gra
     for (int i = 0; i < n_vocab; ++i) mask_out[i] = logits[(size_t) i] != 0.0f ? 1 : 0;
     return (int) g.stacks.size();
 }
+
+// The reference's VAD pre-pass (static whisper_vad, whisper.cpp:6615-6793) on the context's default state: runs its Silero graph on
+// `samples`, filters them, builds the state's time-mapping table.  out[cap] receives the filtered samples, table[2 * table_cap] the
+// (processed, original) pairs, map_in[n_map] -> map_out through map_processed_to_original_time (whisper.cpp:7882-7925).
+// Returns the number of filtered samples (0 when it found no speech), -1 on failure.
+extern "C" int ref_probe_vad_filter(struct whisper_context * ctx, struct whisper_full_params params, const float * samples, int n_samples,
+                                    float * out, int cap, int64_t * table, int table_cap, int * n_table, const int64_t * map_in,
+                                    int64_t * map_out, int n_map) {
+    whisper_state * st = ctx->state;
+    if (st == nullptr) return -1;
+    std::vector<float> filtered;
+    if (!whisper_vad(ctx, st, params, samples, n_samples, filtered)) return -1;
+    const auto & tab = st->vad_mapping_table;
+    *n_table = (int) tab.size();
+    for (int i = 0; i < (int) tab.size() && i < table_cap; ++i) {
+        table[2 * i] = tab[(size_t) i].processed_time;
+        table[2 * i + 1] = tab[(size_t) i].original_time;
+    }
+    if (out) memcpy(out, filtered.data(), std::min(filtered.size(), (size_t) std::max(cap, 0)) * sizeof(float));
+    for (int i = 0; i < n_map; ++i)
+        map_out[i] = (st->has_vad_segments && !tab.empty()) ? map_processed_to_original_time(map_in[i], tab) : map_in[i];
+    return st->has_vad_segments ? (int) filtered.size() : 0;
+}

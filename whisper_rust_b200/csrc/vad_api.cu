@@ -223,6 +223,10 @@ void whisper_vad_free(struct whisper_vad_context * ctx) { delete ctx; }
 
 namespace wb {
 
+bool vad_filter_segments(const whisper_vad_segments & seg_list, float samples_overlap, const float * samples, int n_samples,
+                         std::vector<float> & filtered, std::vector<State::VadMap> & mapping);
+int64_t vad_map_time_table(const std::vector<State::VadMap> & tab, int64_t t);
+
 void vad_state_release(State & st) {
     whisper_vad_free((whisper_vad_context *) st.vad_context);
     st.vad_context = nullptr;
@@ -247,10 +251,19 @@ bool vad_filter(Context * ctx, State * st, const whisper_full_params & params, c
     const whisper_vad_params & vp = params.vad_params;
     whisper_vad_segments * segs = whisper_vad_segments_from_samples(vctx, vp, samples, n_samples);
     if (!segs) return false;
+    st->has_vad_segments = vad_filter_segments(*segs, vp.samples_overlap, samples, n_samples, filtered, st->vad_mapping);
+    whisper_vad_free_segments(segs);
+    return true;
+}
+
+// The host half of whisper_vad: segments (centiseconds) -> filtered samples + mapping table.  Returns whether there were segments
+// (no segments: `filtered` and `mapping` are left untouched, wc:6643-6645).
+bool vad_filter_segments(const whisper_vad_segments & seg_list, float samples_overlap, const float * samples, int n_samples,
+                         std::vector<float> & filtered, std::vector<State::VadMap> & mapping) {
+    const whisper_vad_segments * segs = &seg_list;
     const int n_seg = (int) segs->data.size();
     if (n_seg > 0) {
-        st->has_vad_segments = true;
-        const int overlap = (int) (vp.samples_overlap * WHISPER_SAMPLE_RATE);
+        const int overlap = (int) (samples_overlap * WHISPER_SAMPLE_RATE);
         const int silence = (int) (0.1 * WHISPER_SAMPLE_RATE);
         int total = 0;
         for (int i = 0; i < n_seg; i++) {
@@ -261,7 +274,7 @@ bool vad_filter(Context * ctx, State * st, const whisper_full_params & params, c
             total += b - a;
         }
         filtered.resize((size_t) std::max(0, total + (n_seg > 1 ? (n_seg - 1) * silence : 0)));
-        auto add = [&](int64_t processed, int64_t original) { st->vad_mapping.push_back({processed, original}); };
+        auto add = [&](int64_t processed, int64_t original) { mapping.push_back({processed, original}); };
         int off = 0;
         for (int i = 0; i < n_seg; i++) {
             int a = cs_to_samples(segs->data[(size_t) i].start);
@@ -298,18 +311,17 @@ bool vad_filter(Context * ctx, State * st, const whisper_full_params & params, c
                 off += silence;
             }
         }
-        std::sort(st->vad_mapping.begin(), st->vad_mapping.end(), [](const State::VadMap & x, const State::VadMap & y) { return x.processed < y.processed; });
-        st->vad_mapping.erase(std::unique(st->vad_mapping.begin(), st->vad_mapping.end(),
-                                          [](const State::VadMap & x, const State::VadMap & y) { return x.processed == y.processed; }),
-                              st->vad_mapping.end());
+        std::sort(mapping.begin(), mapping.end(), [](const State::VadMap & x, const State::VadMap & y) { return x.processed < y.processed; });
+        mapping.erase(std::unique(mapping.begin(), mapping.end(),
+                                  [](const State::VadMap & x, const State::VadMap & y) { return x.processed == y.processed; }),
+                      mapping.end());
     }
-    whisper_vad_free_segments(segs);
-    return true;
+    return n_seg > 0;
 }
 
 // map_processed_to_original_time (wc:7882-7925): clamp outside the table, exact hits, integer linear interpolation between points
-int64_t vad_map_time(const State & st, int64_t t) {
-    const auto & tab = st.vad_mapping;
+int64_t vad_map_time(const State & st, int64_t t) { return vad_map_time_table(st.vad_mapping, t); }
+int64_t vad_map_time_table(const std::vector<State::VadMap> & tab, int64_t t) {
     if (tab.empty()) return t;
     if (t <= tab.front().processed) return tab.front().original;
     if (t >= tab.back().processed) return tab.back().original;
@@ -322,3 +334,31 @@ int64_t vad_map_time(const State & st, int64_t t) {
 }
 
 }  // namespace wb
+
+// Host logic of whisper_vad without a device (tests): speech segments from the context's current probabilities (see
+// whisper_b200_test_vad_set_probs), then the sample filter and the time-mapping table.  out[cap] receives the filtered samples,
+// table[2 * table_cap] the (processed, original) pairs; map_in[n_map] -> map_out[n_map] through the table.  Returns the number of
+// filtered samples (0 with *n_table = 0 when there is no speech segment), or -1.
+extern "C" int whisper_b200_test_vad_filter(struct whisper_vad_context * vctx, struct whisper_vad_params params, const float * samples, int n_samples,
+                                            float * out, int cap, int64_t * table, int table_cap, int * n_table, const int64_t * map_in,
+                                            int64_t * map_out, int n_map) {
+    try {
+        if (!vctx || !samples || n_samples < 0 || !n_table) return -1;
+        whisper_vad_segments * segs = whisper_vad_segments_from_probs(vctx, params);
+        if (!segs) return -1;
+        std::vector<float> filtered;
+        std::vector<wb::State::VadMap> mapping;
+        const bool any = wb::vad_filter_segments(*segs, params.samples_overlap, samples, n_samples, filtered, mapping);
+        whisper_vad_free_segments(segs);
+        *n_table = (int) mapping.size();
+        for (int i = 0; i < (int) mapping.size() && i < table_cap && table; ++i) {
+            table[2 * i] = mapping[(size_t) i].processed;
+            table[2 * i + 1] = mapping[(size_t) i].original;
+        }
+        if (out) memcpy(out, filtered.data(), std::min(filtered.size(), (size_t) std::max(cap, 0)) * sizeof(float));
+        for (int i = 0; i < n_map && map_in && map_out; ++i) map_out[i] = any ? wb::vad_map_time_table(mapping, map_in[i]) : map_in[i];
+        return (int) filtered.size();
+    } catch (...) {
+        return -1;
+    }
+}
