@@ -114,6 +114,17 @@ WHISPER_API int whisper_b200_test_gemm_wcluster(const void * w_f16, const void *
 WHISPER_API int whisper_b200_test_vad_filter(struct whisper_vad_context * vctx, struct whisper_vad_params params, const float * samples,
                                              int n_samples, float * out, int cap, int64_t * table, int table_cap, int * n_table,
                                              const int64_t * map_in, int64_t * map_out, int n_map);
+/* Host logic without a device (tests; replaces whisper_exp_compute_token_level_timestamps wc:8390-8615 and whisper_wrap_segment
+ * wc:6049-6100): heuristic token times and segment wrapping applied to caller-supplied segments in order, as whisper_full applies them
+ * to each new segment (wc:7615-7630; max_len <= 0: no wrapping).  Segment s owns seg_n_tokens[s] consecutive entries of tokens[];
+ * energy[n_energy] is the smoothed |signal| of the clip (wc:8359-8388).  The resulting segments come back flattened the same way.
+ * Returns their number, or -1. */
+WHISPER_API int whisper_b200_test_token_timestamps(const char * const * token_texts, int n_vocab, int token_eot, int token_beg,
+                                                   const float * energy, int n_energy, const whisper_token_data * tokens,
+                                                   const int * seg_n_tokens, const int64_t * seg_t0, const int64_t * seg_t1, int n_segments,
+                                                   float thold_pt, float thold_ptsum, int max_len, int split_on_word,
+                                                   whisper_token_data * out_tokens, int out_cap_tokens, int64_t * out_t0, int64_t * out_t1,
+                                                   int * out_n_tokens, int out_cap_segments);
 /* Host only (tests): expand n_elements of a quantised ggml tensor (type ids of ggml.h: 2 q4_0, 3 q4_1, 6 q5_0, 7 q5_1, 8 q8_0, 10..14
  * q2_K..q6_K) to f32 exactly as the model loader does before rounding to f16 (replaces dequantize_row_*, ggml/src/ggml-quants.c:
  * 260-420, 706-1720).  Returns 0, or 1 for a type this loader does not expand / a partial block. */

@@ -154,3 +154,42 @@ extern "C" int ref_probe_vad_filter(struct whisper_context * ctx, struct whisper
         map_out[i] = (st->has_vad_segments && !tab.empty()) ? map_processed_to_original_time(map_in[i], tab) : map_in[i];
     return st->has_vad_segments ? (int) filtered.size() : 0;
 }
+
+// Heuristic token timestamps + segment wrapping (static whisper_exp_compute_token_level_timestamps, whisper.cpp:8390-8615, and
+// whisper_wrap_segment, whisper.cpp:6049-6100) on caller-supplied segments, applied the way whisper_full_with_state applies them to
+// each new segment (whisper.cpp:7615-7630).  `state` is a scratch state of `ctx`: its result_all / energy / t_beg.. are overwritten.
+// Same flattened in/out layout as whisper_b200_test_token_timestamps.  Returns the number of output segments or -1.
+extern "C" int ref_probe_token_timestamps(struct whisper_context * ctx, struct whisper_state * state, const float * energy, int n_energy,
+                                          const whisper_token_data * tokens, const int * seg_n_tokens, const int64_t * seg_t0,
+                                          const int64_t * seg_t1, int n_segments, float thold_pt, float thold_ptsum, int max_len,
+                                          int split_on_word, whisper_token_data * out_tokens, int out_cap_tokens, int64_t * out_t0,
+                                          int64_t * out_t1, int * out_n_tokens, int out_cap_segments) {
+    state->energy.assign(energy, energy + n_energy);
+    state->result_all.clear();
+    state->t_beg = 0;
+    state->t_last = 0;
+    state->tid_last = 0;
+    for (int s = 0, at = 0; s < n_segments; at += seg_n_tokens[s], ++s) {
+        state->result_all.push_back({});
+        auto & seg = state->result_all.back();
+        seg.t0 = seg_t0[s];
+        seg.t1 = seg_t1[s];
+        seg.tokens.assign(tokens + at, tokens + at + seg_n_tokens[s]);
+        seg.speaker_turn_next = false;
+        whisper_exp_compute_token_level_timestamps(*ctx, *state, (int) state->result_all.size() - 1, thold_pt, thold_ptsum);
+        if (max_len > 0) whisper_wrap_segment(*ctx, *state, max_len, split_on_word != 0);
+    }
+    const auto & all = state->result_all;
+    if ((int) all.size() > out_cap_segments) return -1;
+    int at = 0;
+    for (size_t k = 0; k < all.size(); ++k) {
+        const int n = (int) all[k].tokens.size();
+        if (at + n > out_cap_tokens) return -1;
+        out_t0[k] = all[k].t0;
+        out_t1[k] = all[k].t1;
+        out_n_tokens[k] = n;
+        for (int j = 0; j < n; ++j) out_tokens[at + j] = all[k].tokens[(size_t) j];
+        at += n;
+    }
+    return (int) all.size();
+}

@@ -18,6 +18,7 @@
 #include <map>
 #include <regex>
 
+#include "../../include/whisper_b200.h"
 #include "engine.h"
 #include "log.h"
 #include "step.cuh"
@@ -952,11 +953,11 @@ static float text_voice_length(const char * text) {  // wc:8335-8357
     return len;
 }
 
-static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment, float thold_pt, float thold_ptsum) {
-    const Vocab & vc = ctx->model.vocab;
-    Segment & seg = st->result_all[(size_t) i_segment];
+// The computation on explicit inputs (the state's t_beg / t_last / tid_last are carried from segment to segment by the caller)
+static void heuristic_token_timestamps_core(const Vocab & vc, Segment & seg, const std::vector<float> & energy, int64_t & t_beg,
+                                            int64_t & t_last, whisper_token & tid_last, float thold_pt, float thold_ptsum) {
     auto & tk = seg.tokens;
-    const int n_samples = (int) st->energy.size(), n = (int) tk.size();
+    const int n_samples = (int) energy.size(), n = (int) tk.size();
     if (n_samples == 0) {
         log_error("%s: no signal data available\n", __func__);
         return;
@@ -976,25 +977,25 @@ static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment,
                 t.t0 = seg_t0;
                 t.t1 = seg_t0;
                 tk[1].t0 = seg_t0;
-                st->t_beg = seg_t0;
-                st->t_last = seg_t0;
-                st->tid_last = vc.token_beg;
+                t_beg = seg_t0;
+                t_last = seg_t0;
+                tid_last = vc.token_beg;
             } else {
-                t.t0 = st->t_last;
+                t.t0 = t_last;
             }
         }
-        const int64_t tt = st->t_beg + 2 * (int64_t) (t.tid - vc.token_beg);
+        const int64_t tt = t_beg + 2 * (int64_t) (t.tid - vc.token_beg);
         t.vlen = text_voice_length(token_str(vc, t.id));
-        if (t.pt > thold_pt && t.ptsum > thold_ptsum && t.tid > st->tid_last && tt <= seg_t1) {
+        if (t.pt > thold_pt && t.ptsum > thold_ptsum && t.tid > tid_last && tt <= seg_t1) {
             if (j > 0) tk[(size_t) j - 1].t1 = tt;
             t.t0 = tt;
-            st->tid_last = t.tid;
+            tid_last = t.tid;
         }
     }
     tk[(size_t) n - 2].t1 = seg_t1;
     tk[(size_t) n - 1].t0 = seg_t1;
     tk[(size_t) n - 1].t1 = seg_t1;
-    st->t_last = seg_t1;
+    t_last = seg_t1;
 
     // ---- runs without a known end share [first.t0, last.t1] in proportion to the voice lengths (wc:8472-8510)
     for (int first = 0; first < n;) {
@@ -1022,7 +1023,7 @@ static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment,
         }
     }
     // ---- energy edges (wc:8529-8593).  Times map to samples RELATIVE to the segment start, as in the reference
-    const std::vector<float> & en = st->energy;
+    const std::vector<float> & en = energy;
     auto to_sample = [&](int64_t t) {
         const int sidx = (int) (((t - seg_t0) * WHISPER_SAMPLE_RATE) / 100);
         return std::max(0, std::min(n_samples - 1, sidx));
@@ -1066,11 +1067,14 @@ static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment,
     }
 }
 
+static void heuristic_token_timestamps(Context * ctx, State * st, int i_segment, float thold_pt, float thold_ptsum) {
+    heuristic_token_timestamps_core(ctx->model.vocab, st->result_all[(size_t) i_segment], st->energy, st->t_beg, st->t_last, st->tid_last,
+                                    thold_pt, thold_ptsum);
+}
+
 // Splits the newest segment so that no piece's text exceeds max_len bytes (optionally only at tokens that start a word);
 // pieces take over the token times computed above.  Returns the number of segments the newest one became.
-static int wrap_last_segment(Context * ctx, State * st, int max_len, bool split_on_word) {
-    const Vocab & vc = ctx->model.vocab;
-    auto & all = st->result_all;
+static int wrap_last_segment_core(const Vocab & vc, std::vector<Segment> & all, int max_len, bool split_on_word) {
     Segment cur = all.back();  // the piece being scanned (a copy: `all` grows underneath)
     int pieces = 1, used = 0;
     std::string text;
@@ -1105,6 +1109,60 @@ static int wrap_last_segment(Context * ctx, State * st, int max_len, bool split_
     all.back().text = std::move(text);
     return pieces;
 }
+static int wrap_last_segment(Context * ctx, State * st, int max_len, bool split_on_word) {
+    return wrap_last_segment_core(ctx->model.vocab, st->result_all, max_len, split_on_word);
+}
+
+}  // namespace wb
+
+// Host logic without a device (tests): heuristic token timestamps and segment wrapping on caller-supplied segments, exactly as
+// whisper_full applies them to each new segment (timestamps, then the wrap when max_len > 0; t_beg / t_last / tid_last carried from
+// segment to segment).  Input: n_segments segments, segment s owning seg_n_tokens[s] consecutive entries of tokens[].  Output: the
+// resulting segments flattened the same way.  Returns the number of output segments, or -1 (capacity / arguments).
+extern "C" int whisper_b200_test_token_timestamps(const char * const * token_texts, int n_vocab, int token_eot, int token_beg, const float * energy,
+                                                  int n_energy, const whisper_token_data * tokens, const int * seg_n_tokens, const int64_t * seg_t0,
+                                                  const int64_t * seg_t1, int n_segments, float thold_pt, float thold_ptsum, int max_len,
+                                                  int split_on_word, whisper_token_data * out_tokens, int out_cap_tokens, int64_t * out_t0,
+                                                  int64_t * out_t1, int * out_n_tokens, int out_cap_segments) {
+    try {
+        if (!token_texts || n_vocab <= 0 || !tokens || !seg_n_tokens || !seg_t0 || !seg_t1 || n_segments < 0 || n_energy < 0) return -1;
+        wb::Vocab vc;
+        vc.n_vocab = n_vocab;
+        vc.token_eot = token_eot;
+        vc.token_beg = token_beg;
+        vc.id_to_token.resize((size_t) n_vocab);
+        for (int i = 0; i < n_vocab; ++i) vc.id_to_token[(size_t) i] = token_texts[i] ? token_texts[i] : "";
+        const std::vector<float> en(energy, energy + (energy ? n_energy : 0));
+        std::vector<wb::Segment> all;
+        int64_t t_beg = 0, t_last = 0;
+        whisper_token tid_last = 0;
+        for (int sgi = 0, at = 0; sgi < n_segments; at += seg_n_tokens[sgi], ++sgi) {
+            wb::Segment sg{};
+            sg.t0 = seg_t0[sgi];
+            sg.t1 = seg_t1[sgi];
+            sg.tokens.assign(tokens + at, tokens + at + seg_n_tokens[sgi]);
+            all.push_back(std::move(sg));
+            wb::heuristic_token_timestamps_core(vc, all.back(), en, t_beg, t_last, tid_last, thold_pt, thold_ptsum);
+            if (max_len > 0) wb::wrap_last_segment_core(vc, all, max_len, split_on_word != 0);
+        }
+        if ((int) all.size() > out_cap_segments) return -1;
+        int at = 0;
+        for (size_t k = 0; k < all.size(); ++k) {
+            const int n = (int) all[k].tokens.size();
+            if (at + n > out_cap_tokens) return -1;
+            out_t0[k] = all[k].t0;
+            out_t1[k] = all[k].t1;
+            out_n_tokens[k] = n;
+            for (int j = 0; j < n; ++j) out_tokens[at + j] = all[k].tokens[(size_t) j];
+            at += n;
+        }
+        return (int) all.size();
+    } catch (...) {
+        return -1;
+    }
+}
+
+namespace wb {
 
 // --------------------------------------------------------------------------------------------
 // F4: language auto-detection (wc:4037-4110): encode at the offset, decode [sot], softmax over the language logits
