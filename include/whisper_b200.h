@@ -125,6 +125,9 @@ WHISPER_API int whisper_b200_test_token_timestamps(const char * const * token_te
                                                    float thold_pt, float thold_ptsum, int max_len, int split_on_word,
                                                    whisper_token_data * out_tokens, int out_cap_tokens, int64_t * out_t0, int64_t * out_t1,
                                                    int * out_n_tokens, int out_cap_segments);
+/* Host only (tests): the DTW alignment-head table of a whisper_alignment_heads_preset (replaces g_aheads, wc:417-443) as (text layer,
+ * head) pairs; returns the number of heads, -1 for NONE / N_TOP_MOST / CUSTOM / unknown */
+WHISPER_API int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap);
 /* Host only (tests): expand n_elements of a quantised ggml tensor (type ids of ggml.h: 2 q4_0, 3 q4_1, 6 q5_0, 7 q5_1, 8 q8_0, 10..14
  * q2_K..q6_K) to f32 exactly as the model loader does before rounding to f16 (replaces dequantize_row_*, ggml/src/ggml-quants.c:
  * 260-420, 706-1720).  Returns 0, or 1 for a type this loader does not expand / a partial block. */

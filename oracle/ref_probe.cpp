@@ -193,3 +193,14 @@ extern "C" int ref_probe_token_timestamps(struct whisper_context * ctx, struct w
     }
     return (int) all.size();
 }
+
+// the reference's alignment-head preset table (g_aheads, whisper.cpp:417-443) as (text layer, head) pairs; -1 when the preset has no table
+extern "C" int ref_probe_aheads_preset(int preset, int * pairs, int cap) {
+    auto it = g_aheads.find((whisper_alignment_heads_preset) preset);
+    if (it == g_aheads.end()) return -1;
+    for (size_t i = 0; i < it->second.n_heads && (int) i < cap; ++i) {
+        pairs[2 * i] = it->second.heads[i].n_text_layer;
+        pairs[2 * i + 1] = it->second.heads[i].n_head;
+    }
+    return (int) it->second.n_heads;
+}

@@ -172,3 +172,22 @@ def test_device_alignment_chain_vs_reference(prod_lib, ref_lib, seconds, seed, n
     # and end to end from the QK rows
     np.testing.assert_array_equal(out2[:L2], ra)
     np.testing.assert_array_equal(out2[L2:2 * L2], rb)
+
+
+def test_alignment_head_preset_tables_equal_the_reference(prod_lib, ref_lib):
+    """DtwModelPreset::{TinyEn .. LargeV3Turbo} (rs/whisper_ctx.rs DtwModelPreset -> whisper_alignment_heads_preset, wh:96-112): the
+    (text layer, head) tables of whisper.cpp:417-443, entry for entry and in order (the slot order of the captured QK rows follows it)"""
+    import ctypes as C
+    import numpy as np
+    for lib, name in ((prod_lib, "whisper_b200_test_aheads_preset"), (ref_lib, "ref_probe_aheads_preset")):
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = C.c_int, [C.c_int, C.c_void_p, C.c_int]
+    n_tables = 0
+    for preset in range(-1, 20):
+        a, b = np.full((64, 2), -7, dtype=np.int32), np.full((64, 2), -7, dtype=np.int32)
+        na = ref_lib.ref_probe_aheads_preset(preset, a.ctypes.data, 64)
+        nb = prod_lib.whisper_b200_test_aheads_preset(preset, b.ctypes.data, 64)
+        assert na == nb, preset
+        np.testing.assert_array_equal(a, b, err_msg=f"preset {preset}")
+        n_tables += int(na > 0)
+    assert n_tables == 12

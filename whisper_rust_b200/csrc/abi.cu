@@ -1128,6 +1128,7 @@ int whisper_b200_test_dequantize(int ggml_type, const void * blocks, int64_t n_e
     return dequantize_tensor(ggml_type, blocks, n_elements, dst) ? 0 : 1;
     WB_CATCH(1)
 }
+int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap) { return alignment_heads_preset(preset, pairs, cap); }
 int whisper_b200_gemm_wstream_noalloc(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int split) {
     WB_TRY
     return gemm_wstream_noalloc((const __half *) w, (const __half *) x, out, n, n_out, k, bias, split);

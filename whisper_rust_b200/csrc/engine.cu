@@ -151,6 +151,16 @@ static const struct { const AH * p; int n; } ah_presets[] = {
 #undef AHP
 }  // namespace
 
+// the preset table alone (tests): (text layer, head) pairs of `preset` in table order; returns their number, -1 for a non-table preset
+int alignment_heads_preset(int preset, int * pairs, int cap) {
+    if (preset < 0 || preset >= (int) (sizeof(ah_presets) / sizeof(ah_presets[0])) || ah_presets[preset].p == nullptr) return -1;
+    for (int i = 0; i < ah_presets[preset].n && i < cap && pairs; ++i) {
+        pairs[2 * i] = ah_presets[preset].p[i].l;
+        pairs[2 * i + 1] = ah_presets[preset].p[i].h;
+    }
+    return ah_presets[preset].n;
+}
+
 // Validates and tabulates the alignment heads (aheads_masks_init wc:1190-1303; order: get_alignment_heads_by_layer wc:8623-8642).
 // Slot numbering = concatenation over layers in layer order, heads in preset order (ggml_concat order, wc:2746-2750).
 static bool setup_alignment_heads(Context & ctx) {

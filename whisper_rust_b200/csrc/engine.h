@@ -209,6 +209,7 @@ bool stage_get_mel(State & st, std::vector<float> & out);
 // Encodes one window of each listed state (mel offsets per state) as one batch, then fills their cross caches.
 bool stage_encode(Context & ctx, State * const * states, const int * mel_offsets, int n_states);
 // VAD front end (vad_api.cu)
+int alignment_heads_preset(int preset, int * pairs, int cap);   // engine.cu: the DTW preset tables (tests)
 bool vad_filter(Context * ctx, State * st, const whisper_full_params & params, const float * samples, int n_samples, std::vector<float> & filtered);
 int64_t vad_map_time(const State & st, int64_t t);
 void vad_state_release(State & st);
