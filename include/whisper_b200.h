@@ -125,6 +125,11 @@ WHISPER_API int whisper_b200_test_token_timestamps(const char * const * token_te
                                                    float thold_pt, float thold_ptsum, int max_len, int split_on_word,
                                                    whisper_token_data * out_tokens, int out_cap_tokens, int64_t * out_t0, int64_t * out_t1,
                                                    int * out_n_tokens, int out_cap_segments);
+/* Host only (tests): the unified self-attention KV cache's cell bookkeeping (replaces whisper_kv_cache_{find_slot, cell_max, seq_rm,
+ * seq_cp, clear}, wc:1049-1167) on a cache of `size` cells, driven by n_ops operations of five ints each: {0} clear, {1, n_tokens, seq,
+ * first pos} find_slot, {2, seq, p0, p1} seq_rm, {3, src, dst, p0, p1} seq_cp, {4} cell_max.  per_op[3 i ..] = {return value, head,
+ * cell_max}; cells_out[2 c ..] = {pos, sequence-id bit mask}.  Returns 0. */
+WHISPER_API int whisper_b200_test_kv_script(int size, const int * ops, int n_ops, int * per_op, int * cells_out);
 /* Host only (tests): the DTW alignment-head table of a whisper_alignment_heads_preset (replaces g_aheads, wc:417-443) as (text layer,
  * head) pairs; returns the number of heads, -1 for NONE / N_TOP_MOST / CUSTOM / unknown */
 WHISPER_API int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap);

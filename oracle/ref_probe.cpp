@@ -204,3 +204,50 @@ extern "C" int ref_probe_aheads_preset(int preset, int * pairs, int cap) {
     }
     return (int) it->second.n_heads;
 }
+
+// The reference's unified self-attention KV cache bookkeeping (static whisper_kv_cache_{find_slot,cell_max,seq_rm,seq_cp},
+// whisper.cpp:1049-1167) driven by a script of operations on a cache of `size` cells with no tensors behind it.
+// ops[5 * i ..]: {0 clear} {1 find_slot: n_tokens, seq, first pos} {2 seq_rm: seq, p0, p1} {3 seq_cp: src, dst, p0, p1} {4 cell_max}
+// per_op[3 * i ..] = {return value (bool / cell_max / 0), head, cell_max after the op}; cells_out[2 * c ..] = {pos, seq-id bit mask}.
+extern "C" int ref_probe_kv_script(int size, const int * ops, int n_ops, int * per_op, int * cells_out) {
+    whisper_kv_cache kv;
+    kv.size = (uint32_t) size;
+    kv.cells.clear();
+    kv.cells.resize((size_t) size);
+    for (int i = 0; i < n_ops; ++i) {
+        const int * o = ops + 5 * i;
+        int ret = 0;
+        if (o[0] == 0) {   // whisper_kv_cache_clear without its ggml_backend_buffer_clear (there is no buffer here)
+            for (auto & c : kv.cells) { c.pos = -1; c.seq_id.clear(); }
+            kv.head = 0;
+        } else if (o[0] == 1) {
+            const int n = o[1];
+            std::vector<whisper_token> tok((size_t) n, 0);
+            std::vector<whisper_pos> pos((size_t) n);
+            std::vector<int32_t> nseq((size_t) n, 1);
+            std::vector<whisper_seq_id> sid((size_t) n, (whisper_seq_id) o[2]);
+            std::vector<whisper_seq_id *> sidp((size_t) n);
+            std::vector<int8_t> lg((size_t) n, 0);
+            for (int k = 0; k < n; ++k) { pos[(size_t) k] = o[3] + k; sidp[(size_t) k] = &sid[(size_t) k]; }
+            whisper_batch b{};
+            b.n_tokens = n; b.token = tok.data(); b.pos = pos.data(); b.n_seq_id = nseq.data(); b.seq_id = sidp.data(); b.logits = lg.data();
+            ret = whisper_kv_cache_find_slot(kv, b) ? 1 : 0;
+        } else if (o[0] == 2) {
+            whisper_kv_cache_seq_rm(kv, o[1], o[2], o[3]);
+        } else if (o[0] == 3) {
+            whisper_kv_cache_seq_cp(kv, o[1], o[2], o[3], o[4]);
+        } else if (o[0] == 4) {
+            ret = whisper_kv_cache_cell_max(kv);
+        }
+        per_op[3 * i] = ret;
+        per_op[3 * i + 1] = (int) kv.head;
+        per_op[3 * i + 2] = whisper_kv_cache_cell_max(kv);
+    }
+    for (int c = 0; c < size; ++c) {
+        cells_out[2 * c] = kv.cells[(size_t) c].pos;
+        int mask = 0;
+        for (auto s : kv.cells[(size_t) c].seq_id) mask |= 1 << s;
+        cells_out[2 * c + 1] = mask;
+    }
+    return 0;
+}

@@ -1128,6 +1128,41 @@ int whisper_b200_test_dequantize(int ggml_type, const void * blocks, int64_t n_e
     return dequantize_tensor(ggml_type, blocks, n_elements, dst) ? 0 : 1;
     WB_CATCH(1)
 }
+// Host only (tests): the self-attention KV cache's cell bookkeeping (engine.cu: KvCache) driven by a script of operations; same
+// encoding as oracle/ref_probe.cpp: ref_probe_kv_script.
+int whisper_b200_test_kv_script(int size, const int * ops, int n_ops, int * per_op, int * cells_out) {
+    WB_TRY
+    if (size <= 0 || !ops || n_ops < 0 || !per_op || !cells_out) return -1;
+    KvCache kv;
+    kv.size = size;
+    kv.cells.assign((size_t) size, KvCell{});
+    for (int i = 0; i < n_ops; ++i) {
+        const int * o = ops + 5 * i;
+        int ret = 0;
+        if (o[0] == 0) {
+            kv.clear();
+        } else if (o[0] == 1) {
+            std::vector<int> pos((size_t) o[1]), seq((size_t) o[1], o[2]);
+            for (int k = 0; k < o[1]; ++k) pos[(size_t) k] = o[3] + k;
+            ret = kv.find_slot(pos.data(), seq.data(), o[1]) ? 1 : 0;
+        } else if (o[0] == 2) {
+            kv.seq_rm(o[1], o[2], o[3]);
+        } else if (o[0] == 3) {
+            kv.seq_cp(o[1], o[2], o[3], o[4]);
+        } else if (o[0] == 4) {
+            ret = kv.cell_max();
+        }
+        per_op[3 * i] = ret;
+        per_op[3 * i + 1] = kv.head;
+        per_op[3 * i + 2] = kv.cell_max();
+    }
+    for (int c = 0; c < size; ++c) {
+        cells_out[2 * c] = kv.cells[(size_t) c].pos;
+        cells_out[2 * c + 1] = (int) kv.cells[(size_t) c].seq;
+    }
+    return 0;
+    WB_CATCH(-1)
+}
 int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap) { return alignment_heads_preset(preset, pairs, cap); }
 int whisper_b200_gemm_wstream_noalloc(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int split) {
     WB_TRY
