@@ -130,6 +130,9 @@ WHISPER_API int whisper_b200_test_token_timestamps(const char * const * token_te
  * first pos} find_slot, {2, seq, p0, p1} seq_rm, {3, src, dst, p0, p1} seq_cp, {4} cell_max.  per_op[3 i ..] = {return value, head,
  * cell_max}; cells_out[2 c ..] = {pos, sequence-id bit mask}.  Returns 0. */
 WHISPER_API int whisper_b200_test_kv_script(int size, const int * ops, int n_ops, int * per_op, int * cells_out);
+/* Host only (tests): the constant tables the loader uploads: gelu_f16[65536] (replaces ggml_table_gelu_f16, G/ggml-cpu/ggml-cpu.c:3515),
+ * sin400 / cos400 / hann400[400] (replace whisper_global_cache, wc:3018-3047).  Null pointers are skipped.  Returns 0. */
+WHISPER_API int whisper_b200_test_host_tables(uint16_t * gelu_f16, float * sin400, float * cos400, float * hann400);
 /* Host only (tests): the DTW alignment-head table of a whisper_alignment_heads_preset (replaces g_aheads, wc:417-443) as (text layer,
  * head) pairs; returns the number of heads, -1 for NONE / N_TOP_MOST / CUSTOM / unknown */
 WHISPER_API int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap);

@@ -251,3 +251,10 @@ extern "C" int ref_probe_kv_script(int size, const int * ops, int n_ops, int * p
     }
     return 0;
 }
+
+// the reference's FFT tables of the mel front end (whisper_global_cache, whisper.cpp:3010-3047): 400 entries each
+extern "C" void ref_probe_mel_tables(float * sn, float * cs, float * hn) {
+    memcpy(sn, global_cache.sin_vals, sizeof(global_cache.sin_vals));
+    memcpy(cs, global_cache.cos_vals, sizeof(global_cache.cos_vals));
+    memcpy(hn, global_cache.hann_window, sizeof(global_cache.hann_window));
+}

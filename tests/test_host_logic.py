@@ -158,3 +158,25 @@ def test_bench_stdout_guard_moves_c_level_output_to_stderr(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
     assert r.stdout.split() == ["before", "after"]
     assert "banner from C" in r.stderr and "py inside" in r.stderr
+
+
+def test_constant_tables_equal_the_reference(prod_lib, ref_lib):
+    """The tables the loader computes on the host and uploads: the 65,536-entry f16 GELU table every MLP and the conv stem read
+    (ggml_table_gelu_f16, G/ggml-cpu/ggml-cpu.c:3515) and the FFT sin / cos / Hann tables of the log-mel kernel (whisper.cpp:3018-3047):
+    bit for bit the reference's own."""
+    import ctypes as C
+    ref_lib.ggml_cpu_init()
+    want_gelu = np.ctypeslib.as_array((C.c_uint16 * 65536).in_dll(ref_lib, "ggml_table_gelu_f16")).copy()
+    ref_lib.ref_probe_mel_tables.restype, ref_lib.ref_probe_mel_tables.argtypes = None, [C.c_void_p] * 3
+    want = [np.zeros(400, dtype=np.float32) for _ in range(3)]
+    ref_lib.ref_probe_mel_tables(*[w.ctypes.data for w in want])
+    prod_lib.whisper_b200_test_host_tables.restype, prod_lib.whisper_b200_test_host_tables.argtypes = C.c_int, [C.c_void_p] * 4
+    got_gelu = np.full(65536, 0xFFFF, dtype=np.uint16)
+    got = [np.full(400, np.nan, dtype=np.float32) for _ in range(3)]
+    assert prod_lib.whisper_b200_test_host_tables(got_gelu.ctypes.data, *[g.ctypes.data for g in got]) == 0
+    assert want_gelu.any()                                                           # the reference's table is initialised
+    finite = np.isfinite(want_gelu.view(np.float16))
+    np.testing.assert_array_equal(got_gelu[finite], want_gelu[finite])
+    assert np.isnan(got_gelu.view(np.float16)[~finite]).sum() == np.isnan(want_gelu.view(np.float16)[~finite]).sum()
+    for name, w, g in zip(("sin", "cos", "hann"), want, got):
+        np.testing.assert_array_equal(g.view(np.uint32), w.view(np.uint32), err_msg=name)

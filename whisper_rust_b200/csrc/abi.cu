@@ -1163,6 +1163,10 @@ int whisper_b200_test_kv_script(int size, const int * ops, int n_ops, int * per_
     return 0;
     WB_CATCH(-1)
 }
+int whisper_b200_test_host_tables(uint16_t * gelu_f16, float * sin400, float * cos400, float * hann400) {
+    host_tables(gelu_f16, sin400, cos400, hann400);
+    return 0;
+}
 int whisper_b200_test_aheads_preset(int preset, int * pairs, int cap) { return alignment_heads_preset(preset, pairs, cap); }
 int whisper_b200_gemm_wstream_noalloc(const void * w, const void * x, float * out, int n, int n_out, int k, const float * bias, int split) {
     WB_TRY

@@ -269,6 +269,27 @@ struct Dest {
 
 }  // namespace
 
+// The constant tables the kernels read, computed on the host exactly as the reference computes its own: the 65,536-entry f16 GELU table
+// (ggml_table_gelu_f16, ggml-cpu.c:3515 over ggml_gelu_f32, ggml-cpu/vec.h:552-554) and the FFT sin / cos / Hann tables of the mel front
+// end (whisper_global_cache, wc:3018-3047).  gelu[65536], sn / cs / hn[400]; any pointer may be null.
+void host_tables(uint16_t * gelu, float * sn, float * cs, float * hn) {
+    if (gelu) {
+        const float GELU_COEF_A = 0.044715f, SQRT_2_OVER_PI = 0.79788456080286535587989211986876f;
+        for (int i = 0; i < 65536; ++i) {
+            const float x = h2f((uint16_t) i);
+            // this translation unit is compiled with -ffp-contract=off like the ISO-C build of the reference's table initialiser
+            const float g = 0.5f * x * (1.0f + tanhf(SQRT_2_OVER_PI * x * (1.0f + GELU_COEF_A * x * x)));
+            gelu[i] = f2h(g);
+        }
+    }
+    for (int i = 0; i < 400; ++i) {
+        const double theta = (2 * M_PI * i) / 400;
+        if (sn) sn[i] = sinf((float) theta);
+        if (cs) cs[i] = cosf((float) theta);
+        if (hn) hn[i] = (float) (0.5 * (1.0 - cosf((float) ((2.0 * M_PI * i) / 400))));
+    }
+}
+
 // the loader's block expansion alone (tests): n elements of ggml type `ggml_type` -> f32; false for a type the loader does not expand
 bool dequantize_tensor(int ggml_type, const void * blocks, int64_t n, float * dst) {
     if (quant_block_bytes(ggml_type) == 0 || n < 0 || (n % quant_block_elems(ggml_type)) != 0 || !blocks || !dst) return false;
@@ -456,22 +477,9 @@ bool load_model(whisper_model_loader * loader, int device, Model & m) {
     // ---------------- tables ----------------
     {
         std::vector<uint16_t> tab(65536);
-        const float GELU_COEF_A = 0.044715f, SQRT_2_OVER_PI = 0.79788456080286535587989211986876f;
-        for (int i = 0; i < 65536; ++i) {
-            const float x = h2f((uint16_t) i);
-            // ggml_gelu_f32 (ggml-cpu/vec.h:552-554); this translation unit is compiled with -ffp-contract=off like the
-            // ISO-C build of the reference's table initialiser (ggml-cpu.c:3515)
-            const float g = 0.5f * x * (1.0f + tanhf(SQRT_2_OVER_PI * x * (1.0f + GELU_COEF_A * x * x)));
-            tab[i] = f2h(g);
-        }
-        WB_CUDA_OK(cudaMemcpy(m.gelu_table, tab.data(), 65536 * 2, cudaMemcpyHostToDevice));
         float sn[400], cs[400], hn[400];
-        for (int i = 0; i < 400; ++i) {  // wc:3031-3047
-            const double theta = (2 * M_PI * i) / 400;
-            sn[i] = sinf((float) theta);
-            cs[i] = cosf((float) theta);
-            hn[i] = (float) (0.5 * (1.0 - cosf((float) ((2.0 * M_PI * i) / 400))));
-        }
+        host_tables(tab.data(), sn, cs, hn);
+        WB_CUDA_OK(cudaMemcpy(m.gelu_table, tab.data(), 65536 * 2, cudaMemcpyHostToDevice));
         WB_CUDA_OK(cudaMemcpy(m.mel_sin, sn, sizeof(sn), cudaMemcpyHostToDevice));
         WB_CUDA_OK(cudaMemcpy(m.mel_cos, cs, sizeof(cs), cudaMemcpyHostToDevice));
         WB_CUDA_OK(cudaMemcpy(m.mel_hann, hn, sizeof(hn), cudaMemcpyHostToDevice));

@@ -101,6 +101,8 @@ struct Model {
 // Streaming loader over the ABI's whisper_model_loader (wh:153-158).  Returns false (with a logged reason) on any
 // malformed input, exactly where the reference's loader would (wc:1513-1965).
 bool load_model(whisper_model_loader * loader, int device, Model & model);
+// host only: the GELU f16 table and the mel front end's sin / cos / Hann tables as load_model uploads them (null pointers are skipped)
+void host_tables(uint16_t * gelu, float * sn, float * cs, float * hn);
 // host only: expand n elements of a quantised ggml type (q4_0 ... q8_0, q2_K ... q6_K) to f32 the way load_model does
 bool dequantize_tensor(int ggml_type, const void * blocks, int64_t n, float * dst);
 
