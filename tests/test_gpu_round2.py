@@ -421,6 +421,24 @@ def test_k_quantised_checkpoint_loads_and_matches(prod_lib, ref_lib, ftype):
         assert int(np.argmax(lq)) == int(np.argmax(lr))
 
 
+@pytest.mark.xfail(strict=False, reason="added after this round's GPU budget was spent: written against the oracle, not yet run on a B200")
+@pytest.mark.parametrize("seconds,seed", [(30.0, 3), (47.3, 5)])
+def test_english_only_vocabulary_matches_oracle(prod_lib, ref_lib, seconds, seed):
+    """*.en checkpoints (n_vocab 51864): special ids unshifted (wc:472-482 vs 1642-1657), the prompt is [sot] alone (wc:6943-6953), the
+    DTW prefix likewise (wc:8801); whole transcripts against the oracle"""
+    pcm = synth.synth_audio(seconds, seed=seed)
+    out = []
+    for lib, gpu in ((ref_lib, False), (prod_lib, True)):
+        ctx = _ctx(lib, "minien", gpu, QREC)
+        assert not ctx.is_multilingual() and ctx.token_eot() == 50256 and ctx.token_sot() == 50257 and ctx.token_beg() == 50363
+        st = ctx.create_state()
+        assert st.full(_params(lib, best_of=1), pcm) == 0
+        out.append(st.segments())
+        st.free(); ctx.free()
+    _assert_same(out[0], out[1], dtw_exact=False)
+    assert sum(len(s.tokens) for s in out[1]) > 0
+
+
 def test_unsupported_quantisation_fails_loudly(prod_lib):
     blob = bytearray(synth.model_bytes("micro", QREC, with_tensors=False))
     blob[4 + 10 * 4:4 + 11 * 4] = (19).to_bytes(4, "little")       # ftype 19 = IQ4_NL: a codebook type, not expanded by the loader

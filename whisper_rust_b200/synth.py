@@ -67,6 +67,8 @@ ARCHS = {
     "distil":   Arch("distil", 51865, 1500, 192, 3, 4, 448, 192, 3, 2, 80),
     "micro":    Arch("micro", 51865, 1500, 128, 2, 2, 448, 128, 2, 2, 80),
     "mini":     Arch("mini", 51865, 1500, 192, 3, 2, 448, 192, 3, 3, 80),
+    # an English-only vocabulary (n_vocab 51864 = the *.en checkpoints): no language / task tokens in the prompt, unshifted special ids
+    "minien":   Arch("minien", 51864, 1500, 192, 3, 2, 448, 192, 3, 3, 80),
     # every row length a multiple of 256: the smallest shape the K-quant block formats (q2_K ... q6_K) can hold
     "minik":    Arch("minik", 51865, 1500, 256, 4, 2, 448, 256, 4, 3, 80),
 }
