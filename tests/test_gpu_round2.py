@@ -421,7 +421,8 @@ def test_k_quantised_checkpoint_loads_and_matches(prod_lib, ref_lib, ftype):
         assert int(np.argmax(lq)) == int(np.argmax(lr))
 
 
-@pytest.mark.xfail(strict=False, reason="added after this round's GPU budget was spent: written against the oracle, not yet run on a B200")
+@pytest.mark.skipif(not __import__("os").environ.get("WB200_RUN_UNVERIFIED"),
+                    reason="added after this round's GPU budget was spent: written against the oracle, not yet run on a B200 (set WB200_RUN_UNVERIFIED=1)")
 @pytest.mark.parametrize("seconds,seed", [(30.0, 3), (47.3, 5)])
 def test_english_only_vocabulary_matches_oracle(prod_lib, ref_lib, seconds, seed):
     """*.en checkpoints (n_vocab 51864): special ids unshifted (wc:472-482 vs 1642-1657), the prompt is [sot] alone (wc:6943-6953), the
